@@ -1,0 +1,259 @@
+"""Host-side mirror of the reference's entry points for its blur hot path.
+
+Same names, argument meaning and in-place behaviour as michelerenzullo/Blur_algorithms
+(Source.cpp / Utils.hpp); the work is done by hand-written sm_100a kernels behind the C ABI in
+include/blur_b200.h.  Images are numpy uint8 arrays [rows, cols, 3] (what cv::imread returns) and
+are modified IN PLACE like `image.data` in the reference; torch CUDA tensors are accepted by the
+`GaussPlan` / `*_device` entry points for device-resident use.
+
+There is no CPU fallback: every compute call needs a CUDA device and raises BlurB200Error
+otherwise.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+
+from . import _lib
+from ._lib import NYQUIST_EXACT, NYQUIST_PFFFT, BlurB200Error, check, lib
+
+__all__ = [
+    "isValidSize", "nearestTransformSize", "gaussian_window", "getGaussian", "gauss_geometry",
+    "pffft_", "pocketfft_1D", "pocketfft_2D", "fastboxblur", "Reflect_101", "deinterleave_BGR",
+    "interleave_BGR", "flip_block", "dft_image", "Test", "GaussPlan", "fastboxblur_device",
+    "kernel_launches", "BlurB200Error", "NYQUIST_EXACT", "NYQUIST_PFFFT",
+]
+
+
+# ---- sizing helpers (host) --------------------------------------------------------------------
+
+def isValidSize(N: int) -> int:
+    """Utils.hpp:141-148."""
+    return lib.blur_b200_is_valid_size(int(N))
+
+
+def nearestTransformSize(N: int) -> int:
+    """Utils.hpp:150-157."""
+    return lib.blur_b200_nearest_transform_size(int(N))
+
+
+def gaussian_window(sigma: float, max_width: int = 0) -> int:
+    """Source.cpp:60-73."""
+    return lib.blur_b200_gaussian_window(float(sigma), int(max_width))
+
+
+def getGaussian(sigma: float, width: int = 0, FFT_length: int = 0) -> np.ndarray:
+    """Source.cpp:75-102.  Returns the float32 taps (rotated so the centre is element 0 when
+    FFT_length is given) instead of filling a caller-provided container."""
+    if not width:
+        width = gaussian_window(sigma)
+    out = np.zeros(max(width, FFT_length), np.float32)
+    check(lib.blur_b200_get_gaussian(out.ctypes.data, float(sigma), int(width), int(FFT_length)))
+    return out
+
+
+def gauss_geometry(rows: int, cols: int, sigma: float) -> dict:
+    """kSize / pad / FFT lengths of the 1-D tile path, Source.cpp:434-457."""
+    o = (C.c_int * 4)()
+    check(lib.blur_b200_gauss_geometry(rows, cols, float(sigma), o))
+    return dict(kSize=o[0], pad=o[1], n_col=o[2], n_row=o[3])
+
+
+# ---- helpers ------------------------------------------------------------------------------------
+
+def _as_image(image: np.ndarray) -> np.ndarray:
+    if not isinstance(image, np.ndarray) or image.dtype != np.uint8 or image.ndim != 3 or image.shape[2] != 3:
+        raise BlurB200Error(_lib.EINVAL, "image must be a numpy uint8 array of shape [rows, cols, 3]")
+    if not image.flags["C_CONTIGUOUS"] or not image.flags["WRITEABLE"]:
+        raise BlurB200Error(_lib.EINVAL, "image must be C-contiguous and writeable (it is modified in place)")
+    return image
+
+
+def _ptr(t) -> int:
+    """data pointer of a torch tensor / numpy array / int"""
+    if isinstance(t, int):
+        return t
+    if isinstance(t, np.ndarray):
+        return t.ctypes.data
+    return t.data_ptr()
+
+
+def _stream() -> int:
+    import torch
+    return torch.cuda.current_stream().cuda_stream
+
+
+# ---- Gaussian blur ------------------------------------------------------------------------------
+
+def pffft_(image: np.ndarray, nsmooth: float) -> None:
+    """pffft_(cv::Mat& image, double nsmooth), Source.cpp:429-570.  In place.  Reproduces the
+    Nyquist-bin behaviour of pffft_sorted_optimized_convolution (Source.cpp:414-427)."""
+    img = _as_image(image)
+    check(lib.blur_b200_gauss_u8c3(img.ctypes.data, img.shape[0], img.shape[1], float(nsmooth), NYQUIST_PFFFT))
+
+
+def pocketfft_1D(image: np.ndarray, nsmooth: float) -> None:
+    """pocketfft_1D(cv::Mat& image, double nsmooth), Source.cpp:280-392.  In place."""
+    img = _as_image(image)
+    check(lib.blur_b200_gauss_u8c3(img.ctypes.data, img.shape[0], img.shape[1], float(nsmooth), NYQUIST_EXACT))
+
+
+def pocketfft_2D(image: np.ndarray, nsmooth: float) -> None:
+    """pocketfft_2D(cv::Mat& image, double nsmooth), Source.cpp:143-277 (blur branch).  In place.
+    The 2-D formulation computes the same separable reflect-101 convolution as pocketfft_1D and
+    differs from it only by float rounding, so it runs on the same kernels."""
+    pocketfft_1D(image, nsmooth)
+
+
+class GaussPlan:
+    """Cached plan (twiddles, separable kernel spectra, workspaces) for device-resident blurs of
+    one (rows, cols, sigma) problem.  Replaces the per-call setup of Source.cpp:465-503."""
+
+    def __init__(self, rows: int, cols: int, sigma: float, nyquist_mode: int = NYQUIST_EXACT,
+                 device: int = 0, rank: int = 0, nranks: int = 1):
+        self._h = C.c_void_p()
+        self.rows, self.cols, self.sigma = rows, cols, float(sigma)
+        self.rank, self.nranks = rank, nranks
+        if nranks == 1:
+            check(lib.blur_b200_gauss_plan_create(C.byref(self._h), rows, cols, float(sigma), nyquist_mode, device))
+        else:
+            check(lib.blur_b200_gauss_plan_create_sharded(C.byref(self._h), rows, cols, float(sigma), nyquist_mode,
+                                                          device, rank, nranks))
+        info = (C.c_int64 * 16)()
+        check(lib.blur_b200_gauss_plan_info(self._h, info))
+        keys = ["kSize", "pad", "n_col", "n_row", "stripe_rows", "cpp", "row0", "valid_rows", "block_floats",
+                "launches_per_run", "threads_row", "threads_col", "batch_row", "batch_col", "smem_row", "smem_col"]
+        self.info = {k: int(v) for k, v in zip(keys, info)}
+
+    def close(self) -> None:
+        if self._h:
+            lib.blur_b200_gauss_plan_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def run(self, d_in, d_out=None, stream: int | None = None):
+        """d_in/d_out: torch uint8 CUDA tensors [rows, cols, 3]; in place if d_out is None."""
+        d_out = d_in if d_out is None else d_out
+        check(lib.blur_b200_gauss_run_device(self._h, _ptr(d_in), _ptr(d_out), _stream() if stream is None else stream))
+        return d_out
+
+    def run_host(self, h_in: np.ndarray, h_out: np.ndarray | None = None):
+        """numpy / pinned host buffers; H2D + kernels + D2H inside the call."""
+        h_out = h_in if h_out is None else h_out
+        check(lib.blur_b200_gauss_run_host(self._h, _ptr(h_in), _ptr(h_out)))
+        return h_out
+
+    def rowpass_f32(self, d_in, d_planar, stream: int | None = None):
+        """float32 row-pass result as planar [3, rows, cols] (parity hook for `resf`, Source.cpp:536)."""
+        check(lib.blur_b200_gauss_rowpass_f32(self._h, _ptr(d_in), _ptr(d_planar), _stream() if stream is None else stream))
+        return d_planar
+
+    def row_pass(self, d_in_stripe, d_q, stream: int | None = None):
+        check(lib.blur_b200_gauss_row_pass(self._h, _ptr(d_in_stripe), _ptr(d_q), _stream() if stream is None else stream))
+
+    def col_pass(self, d_q_chunks, d_out_cols, stream: int | None = None):
+        check(lib.blur_b200_gauss_col_pass(self._h, _ptr(d_q_chunks), _ptr(d_out_cols), _stream() if stream is None else stream))
+
+
+# ---- FastBoxBlur --------------------------------------------------------------------------------
+
+def fastboxblur(image: np.ndarray, w: int, h: int, channels: int, ksize: int, passes: int) -> None:
+    """fastboxblur(in, w, h, channels, ksize, passes), call site Source.cpp:587.  In place on a
+    uint8 buffer of h*w*channels bytes."""
+    if not isinstance(image, np.ndarray) or image.dtype != np.uint8 or image.size != w * h * channels:
+        raise BlurB200Error(_lib.EINVAL, "image must be a numpy uint8 buffer of w*h*channels bytes")
+    if not image.flags["C_CONTIGUOUS"] or not image.flags["WRITEABLE"]:
+        raise BlurB200Error(_lib.EINVAL, "image must be C-contiguous and writeable")
+    check(lib.blur_b200_fastboxblur(image.ctypes.data, w, h, channels, int(ksize), int(passes)))
+
+
+def fastboxblur_device(d_img, w: int, h: int, channels: int, ksize: int, passes: int, batch: int, d_scratch,
+                       stream: int | None = None) -> None:
+    """Device-resident, batched variant: d_img is `batch` images back to back."""
+    check(lib.blur_b200_fastboxblur_device(_ptr(d_img), w, h, channels, int(ksize), int(passes), batch,
+                                           _ptr(d_scratch), _stream() if stream is None else stream))
+
+
+# ---- layout utilities ---------------------------------------------------------------------------
+
+def Reflect_101(image: np.ndarray, pad_top: int, pad_bottom: int, pad_left: int, pad_right: int) -> np.ndarray:
+    """Reflect_101<uint8_t,C>(input, output, top, bottom, left, right, original_size),
+    Utils.hpp:212-243.  Returns the padded array (pads are clamped to dim-1 like the reference)."""
+    if image.dtype != np.uint8 or image.ndim not in (2, 3):
+        raise BlurB200Error(_lib.EINVAL, "image must be uint8 [rows, cols] or [rows, cols, C]")
+    img = np.ascontiguousarray(image)
+    rows, cols = img.shape[:2]
+    ch = 1 if img.ndim == 2 else img.shape[2]
+    if min(pad_top, pad_bottom, pad_left, pad_right) < 0:
+        raise BlurB200Error(_lib.EINVAL, "negative pad")
+    t, b = min(pad_top, rows - 1), min(pad_bottom, rows - 1)
+    l, r = min(pad_left, cols - 1), min(pad_right, cols - 1)
+    out = np.empty((rows + t + b, cols + l + r, ch), np.uint8)
+    sz = (C.c_int * 2)(rows, cols)
+    check(lib.blur_b200_reflect_101_u8_host(img.ctypes.data, out.ctypes.data, pad_top, pad_bottom, pad_left,
+                                            pad_right, sz, ch))
+    return out if img.ndim == 3 else out[..., 0]
+
+
+def deinterleave_BGR(d_interleaved, d_planes, total: int, stream: int | None = None) -> None:
+    """deinterleave_BGR<uint8_t,float>, Utils.hpp:159-184.  d_planes: float32 CUDA tensor [3, total]."""
+    check(lib.blur_b200_deinterleave_u8_f32(_ptr(d_interleaved), _ptr(d_planes[0]), _ptr(d_planes[1]),
+                                            _ptr(d_planes[2]), total, _stream() if stream is None else stream))
+
+
+def interleave_BGR(d_planes, d_interleaved, total: int, stream: int | None = None) -> None:
+    """interleave_BGR<uint8_t,float>, Utils.hpp:186-210 (+0.5f, truncation)."""
+    check(lib.blur_b200_interleave_f32_u8(_ptr(d_planes[0]), _ptr(d_planes[1]), _ptr(d_planes[2]),
+                                          _ptr(d_interleaved), total, _stream() if stream is None else stream))
+
+
+def flip_block(d_in, d_out, w: int, h: int, stream: int | None = None) -> None:
+    """flip_block<float,1>(in, out, w, h): in is h x w, out is w x h (Source.cpp:540,562)."""
+    check(lib.blur_b200_flip_block_f32(_ptr(d_in), _ptr(d_out), w, h, _stream() if stream is None else stream))
+
+
+# ---- DFT_image ----------------------------------------------------------------------------------
+
+def dft_image(image: np.ndarray, nsmooth: float = 0.1, want_f32: bool = False):
+    """pocketfft_2D built with `#define DFT_image` (Source.cpp:240-252, 268-276): returns the
+    uint8 spectrum image 20*log10(|Re F| + 1e-5) (fft-shifted, cropped to the input size), and
+    with want_f32 also the float spectrum of the padded planes [3, H, W]."""
+    img = _as_image(np.ascontiguousarray(image).copy())
+    rows, cols = img.shape[:2]
+    padded = (C.c_int * 2)()
+    border = (C.c_int * 4)()
+    check(lib.blur_b200_dft_image_sizes(rows, cols, float(nsmooth), padded, border))
+    out = np.empty_like(img)
+    spec = np.empty((3, padded[0], padded[1]), np.float32) if want_f32 else None
+    check(lib.blur_b200_dft_image_host(img.ctypes.data, out.ctypes.data, rows, cols, float(nsmooth),
+                                       spec.ctypes.data if want_f32 else None, padded))
+    return (out, spec) if want_f32 else out
+
+
+# ---- dispatcher ---------------------------------------------------------------------------------
+
+def Test(image: np.ndarray, flag: int = 0, nsmooth: float = 5) -> None:
+    """Test(cv::Mat& image, int flag, double nsmooth), Source.cpp:574-608: 5 pocketfft_1D,
+    4 fastboxblur (ksize = nsmooth*nsmooth, 2 passes), 3 pffft_, 2 pocketfft_2D.  Flag 1 (the
+    OpenCV comparison line) is outside the hot path and raises."""
+    if flag == 5:
+        pocketfft_1D(image, nsmooth)
+    elif flag == 4:
+        img = _as_image(image)
+        fastboxblur(img, img.shape[1], img.shape[0], 3, int(nsmooth * nsmooth), 2)
+    elif flag == 3:
+        pffft_(image, nsmooth)
+    elif flag == 2:
+        pocketfft_2D(image, nsmooth)
+    else:
+        raise BlurB200Error(_lib.EINVAL, "flag 1 (cv::GaussianBlur / cv::blur) is not part of the hot path")
+
+
+def kernel_launches() -> int:
+    return int(lib.blur_b200_kernel_launches())

@@ -1,0 +1,709 @@
+// blur_b200.cu — C ABI (include/blur_b200.h), plan management and the auxiliary kernels.
+//
+// Hot-path kernels: fft_conv_kernel<RowIO>/<ColIO> (fft_kernels.cuh) plus interleave_u8_kernel,
+// boxblur_h_kernel / boxblur_v_kernel below.  No cuFFT, no library calls on the measured path,
+// no CPU fallback: every compute entry point needs a CUDA device.
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdio>
+#include <cstring>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/blur_b200.h"
+#include "fft_launch.hpp"
+#include "fft_plan.hpp"
+
+using namespace blurb200;
+
+namespace {
+
+std::atomic<uint64_t> g_launches{0};
+thread_local std::string g_cuda_err;
+
+#define CU_TRY(expr)                                                                           \
+    do {                                                                                       \
+        cudaError_t _e = (expr);                                                               \
+        if (_e != cudaSuccess) {                                                               \
+            g_cuda_err = std::string(#expr) + ": " + cudaGetErrorString(_e);                   \
+            return BLUR_B200_ECUDA;                                                            \
+        }                                                                                      \
+    } while (0)
+
+inline int cdiv(int a, int b) { return (a + b - 1) / b; }
+
+// ------------------------------------------------------------------ auxiliary kernels
+
+// U [3][ucols][rows] (uint8, planar, transposed)  ->  out [rows][out_cols][3] (interleaved).
+// Tile: 32 columns x 128 rows x 3 channels through shared memory.  Replaces the reference's
+// second flip_block (Source.cpp:562) and interleave_BGR (:567) for data that is already uint8.
+constexpr int kIlTileC = 32, kIlTileR = 128;
+__global__ void __launch_bounds__(256)
+interleave_u8_kernel(const uint8_t* __restrict__ u, uint8_t* __restrict__ out, int rows, int ucols,
+                     int ncols /* valid columns to emit */, int out_cols /* row pitch of out, in pixels */)
+{
+    __shared__ uint8_t tile[3][kIlTileC][kIlTileR + 4];
+    const int c0 = blockIdx.x * kIlTileC, r0 = blockIdx.y * kIlTileR;
+    const int tid = threadIdx.x;
+    const bool vec = (rows & 3) == 0;
+    // load: each warp takes one (channel, column) line of 128 rows; lane reads 4 rows
+    for (int line = tid >> 5; line < 3 * kIlTileC; line += 8) {
+        const int ch = line / kIlTileC, c = line - ch * kIlTileC;
+        const int lane = tid & 31;
+        const int col = c0 + c;
+        if (col >= ncols) continue;
+        const uint8_t* src = u + (static_cast<size_t>(ch) * ucols + col) * rows + r0;
+        if (vec && r0 + kIlTileR <= rows) {
+            const uchar4 v = *reinterpret_cast<const uchar4*>(src + 4 * lane);
+            *reinterpret_cast<uchar4*>(&tile[ch][c][4 * lane]) = v;
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int r = 4 * lane + k;
+                if (r0 + r < rows) tile[ch][c][r] = src[r];
+            }
+        }
+    }
+    __syncthreads();
+    // store: each row of the tile is (up to) 96 contiguous bytes
+    const int nc = min(kIlTileC, ncols - c0);
+    const int nbytes = nc * 3;
+    for (int idx = tid; idx < kIlTileR * 96; idx += 256) {
+        const int r = idx / 96, b = idx - r * 96;
+        if (b >= nbytes || r0 + r >= rows) continue;
+        const int c = b / 3, ch = b - c * 3;
+        out[(static_cast<size_t>(r0 + r) * out_cols + c0) * 3 + b] = tile[ch][c][r];
+    }
+}
+
+// Q [part][3][cpp][qrows][2] -> planar float [3][rows][cols]   (parity hook only)
+__global__ void q_to_planar_kernel(const float* __restrict__ q, float* __restrict__ planar, int rows, int cols,
+                                   int cpp, int qrows)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int r = blockIdx.y, ch = blockIdx.z;
+    if (x >= cols) return;
+    const int cp = x >> 1, part = cp / cpp, cpl = cp - part * cpp;
+    planar[(static_cast<size_t>(ch) * rows + r) * cols + x] =
+        q[((static_cast<size_t>(part * 3 + ch) * cpp + cpl) * qrows + r) * 2 + (x & 1)];
+}
+
+// Reflect_101<uint8_t,C> (Utils.hpp:212-243): one thread per output byte.
+__global__ void reflect101_u8_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int rows, int cols,
+                                     int C, int top, int bottom, int left, int right)
+{
+    const int prow = rows + top + bottom, pcolb = (cols + left + right) * C;
+    const int b = blockIdx.x * blockDim.x + threadIdx.x;
+    const int i = blockIdx.y;
+    if (b >= pcolb || i >= prow) return;
+    const int px = b / C, c = b - px * C;
+    int sr = i - top;
+    if (sr < 0) sr = -sr;
+    if (sr >= rows) sr = 2 * (rows - 1) - sr;
+    int sx = px - left;
+    if (sx < 0) sx = -sx;
+    if (sx >= cols) sx = 2 * (cols - 1) - sx;
+    out[static_cast<size_t>(i) * pcolb + b] = in[(static_cast<size_t>(sr) * cols + sx) * C + c];
+}
+
+// deinterleave_BGR<uint8_t,float> (Utils.hpp:159-184)
+__global__ void deinterleave_u8_f32_kernel(const uint8_t* __restrict__ in, float* __restrict__ b, float* __restrict__ g,
+                                           float* __restrict__ r, uint32_t total)
+{
+    const uint32_t x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= total) return;
+    b[x] = in[3 * static_cast<size_t>(x) + 0];
+    g[x] = in[3 * static_cast<size_t>(x) + 1];
+    r[x] = in[3 * static_cast<size_t>(x) + 2];
+}
+
+// interleave_BGR<uint8_t,float> (Utils.hpp:186-210): +0.5f, truncation
+__global__ void interleave_f32_u8_kernel(const float* __restrict__ b, const float* __restrict__ g,
+                                         const float* __restrict__ r, uint8_t* __restrict__ out, uint32_t total)
+{
+    const uint32_t x = blockIdx.x * blockDim.x + threadIdx.x;
+    if (x >= total) return;
+    out[3 * static_cast<size_t>(x) + 0] = ColIO::to_u8(b[x]);
+    out[3 * static_cast<size_t>(x) + 1] = ColIO::to_u8(g[x]);
+    out[3 * static_cast<size_t>(x) + 2] = ColIO::to_u8(r[x]);
+}
+
+// flip_block<float,1>: in h x w -> out w x h, 32x32 tiles through padded shared memory
+__global__ void transpose_f32_kernel(const float* __restrict__ in, float* __restrict__ out, int w, int h)
+{
+    __shared__ float tile[32][33];
+    const int x0 = blockIdx.x * 32, y0 = blockIdx.y * 32;
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        const int x = x0 + threadIdx.x, y = y0 + j;
+        if (x < w && y < h) tile[j][threadIdx.x] = in[static_cast<size_t>(y) * w + x];
+    }
+    __syncthreads();
+    for (int j = threadIdx.y; j < 32; j += blockDim.y) {
+        const int y = y0 + threadIdx.x, x = x0 + j;
+        if (x < w && y < h) out[static_cast<size_t>(x) * h + y] = tile[threadIdx.x][j];
+    }
+}
+
+// ------------------------------------------------------------------ box blur kernels
+// Declared semantics: out = (2*sum + k) / (2k), sum over the reflect-101 window.
+
+struct DivK {
+    uint32_t k, d, magic;   // d = 2k ; magic = ceil(2^32 / d), exact while (511k)*(2k) < 2^32
+    int use_magic;
+};
+__device__ __forceinline__ uint32_t box_round(uint32_t sum, const DivK& dk)
+{
+    const uint32_t n = 2u * sum + dk.k;
+    return dk.use_magic ? __umulhi(n, dk.magic) : n / dk.d;
+}
+
+__device__ __forceinline__ int cdiv_dev(int a, int b) { return (a + b - 1) / b; }
+
+__device__ __forceinline__ int refl101(int i, int L)
+{
+    if (i < 0) i = -i;
+    if (i >= L) i = 2 * (L - 1) - i;
+    return i;
+}
+
+// Horizontal pass: one CTA per image row.  The row, extended by r reflected pixels on each side,
+// is staged in shared memory as uint32; a block-wide prefix sum per channel (warp shuffles inside
+// each warp, one shared array across warps) turns every window sum into a difference of two
+// prefix values.
+__global__ void __launch_bounds__(256)
+boxblur_h_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int w, int h, int C, int r, DivK dk,
+                 size_t img_stride)
+{
+    extern __shared__ uint32_t pre[];                 // (w + 2r) * C prefix values
+    __shared__ uint32_t warp_tot[8][4];
+    const int y = blockIdx.x;
+    const uint8_t* row = in + blockIdx.y * img_stride + static_cast<size_t>(y) * w * C;
+    uint8_t* orow = out + blockIdx.y * img_stride + static_cast<size_t>(y) * w * C;
+    const int E = w + 2 * r;                            // extended length in pixels
+    const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+
+    // 1. extended row into shared memory
+    for (int e = tid; e < E * C; e += 256) {
+        const int j = e / C, c = e - j * C;
+        pre[e] = row[refl101(j - r, w) * C + c];
+    }
+    __syncthreads();
+
+    // 2. per-channel inclusive prefix sum: thread t owns pixels [t*ppt, (t+1)*ppt)
+    const int ppt = cdiv_dev(E, 256);
+    const int j0 = min(tid * ppt, E), j1 = min(j0 + ppt, E);
+    uint32_t acc[4] = {0, 0, 0, 0};
+    for (int j = j0; j < j1; ++j)
+        for (int c = 0; c < C; ++c) {
+            acc[c] += pre[j * C + c];
+            pre[j * C + c] = acc[c];
+        }
+    uint32_t off[4];
+    for (int c = 0; c < C; ++c) {
+        uint32_t v = acc[c];
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t n = __shfl_up_sync(0xffffffffu, v, d);
+            if (lane >= d) v += n;
+        }
+        if (lane == 31) warp_tot[wid][c] = v;
+        off[c] = v - acc[c];                             // exclusive within the warp
+    }
+    __syncthreads();
+    for (int c = 0; c < C; ++c)
+        for (int k = 0; k < wid; ++k) off[c] += warp_tot[k][c];
+    for (int j = j0; j < j1; ++j)
+        for (int c = 0; c < C; ++c) pre[j * C + c] += off[c];
+    __syncthreads();
+
+    // 3. window sums: sum(x) = P[x + 2r] - P[x - 1]
+    for (int e = tid; e < w * C; e += 256) {
+        const int x = e / C, c = e - x * C;
+        const uint32_t hi = pre[(x + 2 * r) * C + c];
+        const uint32_t lo = x ? pre[(x - 1) * C + c] : 0u;
+        orow[e] = static_cast<uint8_t>(box_round(hi - lo, dk));
+    }
+}
+
+// Vertical pass: one thread per byte column (4 adjacent bytes per thread when the row pitch is a
+// multiple of 4), sliding accumulator down a segment of `seg` rows.
+template <int V>
+__global__ void __launch_bounds__(128)
+boxblur_v_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int pitch /* w*C bytes */, int h, int r,
+                 DivK dk, int seg, size_t img_stride)
+{
+    const int b = (blockIdx.x * blockDim.x + threadIdx.x) * V;
+    if (b >= pitch) return;
+    const int y0 = blockIdx.y * seg, y1 = min(y0 + seg, h);
+    const uint8_t* src = in + blockIdx.z * img_stride + b;
+    uint8_t* dst = out + blockIdx.z * img_stride + b;
+    uint32_t acc[V];
+#pragma unroll
+    for (int v = 0; v < V; ++v) acc[v] = 0;
+    auto ld = [&](int y, uint32_t* o) {
+        const uint8_t* p = src + static_cast<size_t>(refl101(y, h)) * pitch;
+        if (V == 4) {
+            const uchar4 q = *reinterpret_cast<const uchar4*>(p);
+            o[0] = q.x; o[1] = q.y; o[2] = q.z; o[3] = q.w;
+        } else {
+            o[0] = p[0];
+        }
+    };
+    for (int i = -r; i <= r; ++i) {
+        uint32_t t[V];
+        ld(y0 + i, t);
+#pragma unroll
+        for (int v = 0; v < V; ++v) acc[v] += t[v];
+    }
+    for (int y = y0; y < y1; ++y) {
+        uint8_t* p = dst + static_cast<size_t>(y) * pitch;
+        if (V == 4) {
+            uchar4 o;
+            o.x = box_round(acc[0], dk); o.y = box_round(acc[1], dk);
+            o.z = box_round(acc[2], dk); o.w = box_round(acc[3], dk);
+            *reinterpret_cast<uchar4*>(p) = o;
+        } else {
+            p[0] = static_cast<uint8_t>(box_round(acc[0], dk));
+        }
+        uint32_t a[V], s[V];
+        ld(y + r + 1, a);
+        ld(y - r, s);
+#pragma unroll
+        for (int v = 0; v < V; ++v) acc[v] += a[v] - s[v];
+    }
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ plan
+
+struct AxisTables {
+    FftGeom g;
+    LaunchShape shape;
+    float2* d_tw = nullptr;
+    float* d_kt = nullptr;
+};
+
+struct blur_b200_plan {
+    int device = 0;
+    int rows = 0, cols = 0;
+    double sigma = 0;
+    int mode = 0;
+    GaussGeometry gg{};
+    int rank = 0, nranks = 1;
+    int stripe_rows = 0, cpp = 0, row0 = 0, valid_rows = 0, valid_ncp = 0;
+    size_t block_floats = 0;          // floats per (stripe, part) block of Q
+    AxisTables row, col;
+    float* d_q = nullptr;             // [nranks] blocks
+    uint8_t* d_u = nullptr;           // [3][2*cpp][rows]
+    uint8_t* d_io = nullptr;          // staging for the host entry point (lazy)
+    float* d_q_recv = nullptr;        // unused on a single GPU
+    int num_sms = 148;
+    cudaStream_t stream = nullptr;
+};
+
+namespace {
+
+int build_axis(AxisTables& ax, int N, double sigma, int ksize, int mode)
+{
+    std::vector<int> ovr;
+    if (const char* e = std::getenv("BLUR_B200_PLAN")) {
+        // "17280:18,30;4096:8,16" -> strided radices per FFT length
+        std::string s(e);
+        size_t pos = 0;
+        while (pos < s.size()) {
+            size_t semi = s.find(';', pos);
+            std::string item = s.substr(pos, semi == std::string::npos ? std::string::npos : semi - pos);
+            size_t colon = item.find(':');
+            if (colon != std::string::npos && std::atoi(item.substr(0, colon).c_str()) == N) {
+                std::string rs = item.substr(colon + 1);
+                size_t p2 = 0;
+                while (p2 < rs.size()) {
+                    size_t comma = rs.find(',', p2);
+                    ovr.push_back(std::atoi(rs.substr(p2, comma == std::string::npos ? std::string::npos : comma - p2).c_str()));
+                    if (comma == std::string::npos) break;
+                    p2 = comma + 1;
+                }
+            }
+            if (semi == std::string::npos) break;
+            pos = semi + 1;
+        }
+    }
+    if (!make_geom(N, ax.g, ovr.empty() ? nullptr : &ovr)) return BLUR_B200_ESIZE;
+    ax.shape = choose_launch(ax.g, kMaxThreads);
+    if (ax.shape.smem_bytes > 227 * 1024) return BLUR_B200_ESIZE;
+    std::vector<float2> tw;
+    make_twiddles(N, tw);
+    std::vector<double> K;
+    kernel_spectrum(sigma, ksize, N, K);
+    std::vector<float> kt;
+    make_kt(ax.g, K, mode, kt);
+    CU_TRY(cudaMalloc(&ax.d_tw, sizeof(float2) * tw.size()));
+    CU_TRY(cudaMalloc(&ax.d_kt, sizeof(float) * kt.size()));
+    CU_TRY(cudaMemcpy(ax.d_tw, tw.data(), sizeof(float2) * tw.size(), cudaMemcpyHostToDevice));
+    CU_TRY(cudaMemcpy(ax.d_kt, kt.data(), sizeof(float) * kt.size(), cudaMemcpyHostToDevice));
+    return BLUR_B200_OK;
+}
+
+int plan_create(blur_b200_plan** out, int rows, int cols, double sigma, int mode, int device, int rank, int nranks)
+{
+    if (!out || rows < 1 || cols < 1 || !(sigma > 0) || (mode != 0 && mode != 1) || nranks < 1 || rank < 0 ||
+        rank >= nranks)
+        return BLUR_B200_EINVAL;
+    *out = nullptr;
+    const GaussGeometry gg = gauss_geometry(rows, cols, sigma);
+    // The reference reads out of bounds when pad > dim-1 in the smaller dimension
+    // (README.md:33-38); deliberate tightening: refuse.
+    if (gg.pad < 0 || gg.pad > rows - 1 || gg.pad > cols - 1) return BLUR_B200_EPAD;
+    CU_TRY(cudaSetDevice(device));
+    blur_b200_plan* p = new (std::nothrow) blur_b200_plan();
+    if (!p) return BLUR_B200_ENOMEM;
+    p->device = device; p->rows = rows; p->cols = cols; p->sigma = sigma; p->mode = mode; p->gg = gg;
+    p->rank = rank; p->nranks = nranks;
+    const int cp_total = (cols + 1) / 2;
+    p->cpp = cdiv(cp_total, nranks);
+    int sr = cdiv(rows, nranks);
+    sr += sr & 1;
+    p->stripe_rows = sr;
+    p->row0 = rank * sr;
+    p->valid_rows = std::max(0, std::min(sr, rows - p->row0));
+    p->valid_ncp = std::max(0, std::min(p->cpp, cp_total - rank * p->cpp));
+    p->block_floats = static_cast<size_t>(3) * p->cpp * sr * 2;
+    int rc = build_axis(p->row, gg.n_row, sigma, gg.ksize, mode);
+    if (rc == BLUR_B200_OK) rc = build_axis(p->col, gg.n_col, sigma, gg.ksize, mode);
+    if (rc != BLUR_B200_OK) { blur_b200_gauss_plan_destroy(p); return rc; }
+    cudaDeviceProp prop;
+    CU_TRY(cudaGetDeviceProperties(&prop, device));
+    p->num_sms = prop.multiProcessorCount;
+    CU_TRY(cudaMalloc(&p->d_q, sizeof(float) * p->block_floats * nranks));
+    CU_TRY(cudaMalloc(&p->d_u, static_cast<size_t>(3) * 2 * p->cpp * rows));
+    CU_TRY(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
+    *out = p;
+    return BLUR_B200_OK;
+}
+
+int run_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, float* d_q, cudaStream_t st)
+{
+    if (p->valid_rows <= 0) return BLUR_B200_OK;
+    RowIO io{};
+    io.in = d_in_stripe; io.q = d_q;
+    io.rows = p->valid_rows; io.cols = p->cols; io.pad = p->gg.pad; io.N = p->row.g.N;
+    io.qrows = p->stripe_rows; io.cpp = p->cpp;
+    io.nunits = cdiv(p->valid_rows, 4) * 6;
+    const LaunchShape& s = p->row.shape;
+    const int grid = std::min(cdiv(io.nunits, s.batch), p->num_sms * s.ctas_per_sm);
+    CU_TRY(launch_fft_row(p->row.g, io, p->row.d_tw, p->row.d_kt, s.batch, grid, s.threads, s.smem_bytes, st));
+    ++g_launches;
+    return BLUR_B200_OK;
+}
+
+int run_col_pass_to_u(blur_b200_plan* p, const float* d_q_chunks, cudaStream_t st)
+{
+    ColIO io{};
+    io.q = reinterpret_cast<const float2*>(d_q_chunks);
+    io.chunk_stride = p->block_floats / 2;
+    io.chunk_rows = p->stripe_rows;
+    io.u = p->d_u;
+    io.rows = p->rows; io.ncp = p->cpp; io.valid_ncp = p->valid_ncp; io.ucols = 2 * p->cpp;
+    io.pad = p->gg.pad; io.N = p->col.g.N;
+    io.nunits = 3 * p->cpp;
+    const LaunchShape& s = p->col.shape;
+    const int grid = std::min(cdiv(io.nunits, s.batch), p->num_sms * s.ctas_per_sm);
+    CU_TRY(launch_fft_col(p->col.g, io, p->col.d_tw, p->col.d_kt, s.batch, grid, s.threads, s.smem_bytes, st));
+    ++g_launches;
+    return BLUR_B200_OK;
+}
+
+int run_interleave(blur_b200_plan* p, uint8_t* d_out, int ncols, int out_cols, cudaStream_t st)
+{
+    if (ncols <= 0) return BLUR_B200_OK;
+    dim3 grid(cdiv(ncols, kIlTileC), cdiv(p->rows, kIlTileR));
+    interleave_u8_kernel<<<grid, 256, 0, st>>>(p->d_u, d_out, p->rows, 2 * p->cpp, ncols, out_cols);
+    CU_TRY(cudaGetLastError());
+    ++g_launches;
+    return BLUR_B200_OK;
+}
+
+}  // namespace
+
+// ------------------------------------------------------------------ C ABI
+
+extern "C" {
+
+const char* blur_b200_strerror(int code)
+{
+    switch (code) {
+    case BLUR_B200_OK: return "ok";
+    case BLUR_B200_EINVAL: return "invalid argument";
+    case BLUR_B200_EPAD: return "kernel half-width exceeds min(rows, cols) - 1";
+    case BLUR_B200_ESIZE: return "FFT length not plannable on one SM (valid sizes up to 28160)";
+    case BLUR_B200_ECUDA: return "CUDA error";
+    case BLUR_B200_ENOMEM: return "out of memory";
+    default: return "unknown error";
+    }
+}
+
+const char* blur_b200_last_cuda_error(void) { return g_cuda_err.c_str(); }
+
+int blur_b200_is_valid_size(int n) { return is_valid_size(n); }
+int blur_b200_nearest_transform_size(int n) { return nearest_transform_size(n); }
+int blur_b200_gaussian_window(double sigma, int max_width) { return gaussian_window(sigma, max_width); }
+
+int blur_b200_get_gaussian(float* kernel, double sigma, int width, int fft_length)
+{
+    if (!kernel || width < 0 || fft_length < 0) return BLUR_B200_EINVAL;
+    std::vector<float> k;
+    get_gaussian(k, sigma, width, fft_length);
+    std::memcpy(kernel, k.data(), sizeof(float) * k.size());
+    return BLUR_B200_OK;
+}
+
+int blur_b200_gauss_geometry(int rows, int cols, double sigma, int out[4])
+{
+    if (!out || rows < 1 || cols < 1) return BLUR_B200_EINVAL;
+    const GaussGeometry g = gauss_geometry(rows, cols, sigma);
+    out[0] = g.ksize; out[1] = g.pad; out[2] = g.n_col; out[3] = g.n_row;
+    return BLUR_B200_OK;
+}
+
+int blur_b200_gauss_plan_create(blur_b200_plan** plan, int rows, int cols, double sigma, int nyquist_mode, int device)
+{
+    return plan_create(plan, rows, cols, sigma, nyquist_mode, device, 0, 1);
+}
+
+int blur_b200_gauss_plan_create_sharded(blur_b200_plan** plan, int rows, int cols, double sigma, int nyquist_mode,
+                                        int device, int rank, int nranks)
+{
+    return plan_create(plan, rows, cols, sigma, nyquist_mode, device, rank, nranks);
+}
+
+void blur_b200_gauss_plan_destroy(blur_b200_plan* p)
+{
+    if (!p) return;
+    cudaSetDevice(p->device);
+    cudaFree(p->row.d_tw); cudaFree(p->row.d_kt);
+    cudaFree(p->col.d_tw); cudaFree(p->col.d_kt);
+    cudaFree(p->d_q); cudaFree(p->d_u); cudaFree(p->d_io);
+    if (p->stream) cudaStreamDestroy(p->stream);
+    delete p;
+}
+
+int blur_b200_gauss_plan_info(const blur_b200_plan* p, int64_t info[16])
+{
+    if (!p || !info) return BLUR_B200_EINVAL;
+    info[0] = p->gg.ksize; info[1] = p->gg.pad; info[2] = p->gg.n_col; info[3] = p->gg.n_row;
+    info[4] = p->stripe_rows; info[5] = p->cpp; info[6] = p->row0; info[7] = p->valid_rows;
+    info[8] = static_cast<int64_t>(p->block_floats);
+    info[9] = 3;
+    info[10] = p->row.shape.threads; info[11] = p->col.shape.threads;
+    info[12] = p->row.shape.batch; info[13] = p->col.shape.batch;
+    info[14] = static_cast<int64_t>(p->row.shape.smem_bytes); info[15] = static_cast<int64_t>(p->col.shape.smem_bytes);
+    return BLUR_B200_OK;
+}
+
+int blur_b200_gauss_run_device(blur_b200_plan* p, const uint8_t* d_in, uint8_t* d_out, void* stream)
+{
+    if (!p || !d_in || !d_out || p->nranks != 1) return BLUR_B200_EINVAL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int rc = run_row_pass(p, d_in, p->d_q, st);
+    if (rc) return rc;
+    rc = run_col_pass_to_u(p, p->d_q, st);
+    if (rc) return rc;
+    return run_interleave(p, d_out, p->cols, p->cols, st);
+}
+
+int blur_b200_gauss_run_host(blur_b200_plan* p, const uint8_t* h_in, uint8_t* h_out)
+{
+    if (!p || !h_in || !h_out || p->nranks != 1) return BLUR_B200_EINVAL;
+    CU_TRY(cudaSetDevice(p->device));
+    const size_t nbytes = static_cast<size_t>(p->rows) * p->cols * 3;
+    if (!p->d_io) CU_TRY(cudaMalloc(&p->d_io, nbytes));
+    CU_TRY(cudaMemcpyAsync(p->d_io, h_in, nbytes, cudaMemcpyHostToDevice, p->stream));
+    int rc = blur_b200_gauss_run_device(p, p->d_io, p->d_io, p->stream);
+    if (rc) return rc;
+    CU_TRY(cudaMemcpyAsync(h_out, p->d_io, nbytes, cudaMemcpyDeviceToHost, p->stream));
+    CU_TRY(cudaStreamSynchronize(p->stream));
+    return BLUR_B200_OK;
+}
+
+int blur_b200_gauss_u8c3(uint8_t* h_bgr, int rows, int cols, double sigma, int nyquist_mode)
+{
+    blur_b200_plan* p = nullptr;
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { g_cuda_err = "cudaGetDevice failed (no CUDA device?)"; return BLUR_B200_ECUDA; }
+    int rc = blur_b200_gauss_plan_create(&p, rows, cols, sigma, nyquist_mode, dev);
+    if (rc) return rc;
+    rc = blur_b200_gauss_run_host(p, h_bgr, h_bgr);
+    blur_b200_gauss_plan_destroy(p);
+    return rc;
+}
+
+int blur_b200_gauss_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, float* d_q, void* stream)
+{
+    if (!p || !d_in_stripe || !d_q) return BLUR_B200_EINVAL;
+    return run_row_pass(p, d_in_stripe, d_q, static_cast<cudaStream_t>(stream));
+}
+
+int blur_b200_gauss_col_pass(blur_b200_plan* p, const float* d_q_chunks, uint8_t* d_out_cols, void* stream)
+{
+    if (!p || !d_q_chunks || !d_out_cols) return BLUR_B200_EINVAL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int rc = run_col_pass_to_u(p, d_q_chunks, st);
+    if (rc) return rc;
+    return run_interleave(p, d_out_cols, 2 * p->cpp, 2 * p->cpp, st);
+}
+
+int blur_b200_gauss_rowpass_f32(blur_b200_plan* p, const uint8_t* d_in, float* d_planar, void* stream)
+{
+    if (!p || !d_in || !d_planar || p->nranks != 1) return BLUR_B200_EINVAL;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    int rc = run_row_pass(p, d_in, p->d_q, st);
+    if (rc) return rc;
+    dim3 grid(cdiv(p->cols, 256), p->rows, 3);
+    q_to_planar_kernel<<<grid, 256, 0, st>>>(p->d_q, d_planar, p->rows, p->cols, p->cpp, p->stripe_rows);
+    CU_TRY(cudaGetLastError());
+    ++g_launches;
+    return BLUR_B200_OK;
+}
+
+// ---- box blur
+
+int blur_b200_fastboxblur_device(uint8_t* d_img, int w, int h, int channels, int ksize, int passes, int batch,
+                                 uint8_t* d_scratch, void* stream)
+{
+    if (!d_img || !d_scratch || w < 1 || h < 1 || channels < 1 || channels > 4 || ksize < 1 || passes < 0 || batch < 1)
+        return BLUR_B200_EINVAL;
+    const int r = (ksize - 1) / 2;
+    if (r > w - 1 || r > h - 1) return BLUR_B200_EPAD;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    DivK dk;
+    dk.k = 2u * static_cast<uint32_t>(r) + 1u;
+    dk.d = 2u * dk.k;
+    dk.magic = static_cast<uint32_t>(((1ull << 32) + dk.d - 1) / dk.d);
+    dk.use_magic = (511ull * dk.k) * dk.d < (1ull << 32) ? 1 : 0;
+    const size_t img_bytes = static_cast<size_t>(w) * h * channels;
+    const size_t smem_h = static_cast<size_t>(w + 2 * r) * channels * sizeof(uint32_t);
+    if (smem_h > 200 * 1024) return BLUR_B200_ESIZE;
+    static size_t configured = 0;
+    if (smem_h > 48 * 1024 && smem_h > configured) {
+        CU_TRY(cudaFuncSetAttribute(boxblur_h_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_h)));
+        configured = smem_h;
+    }
+    const int pitch = w * channels;
+    const bool vec = (pitch % 4 == 0) && (reinterpret_cast<uintptr_t>(d_img) % 4 == 0) &&
+                     (reinterpret_cast<uintptr_t>(d_scratch) % 4 == 0) && (img_bytes % 4 == 0);
+    const int seg = 64;
+    // Keep each group's image + scratch resident in L2 across the 2*passes sweeps.
+    const size_t l2_budget = 48ull << 20;
+    int group = static_cast<int>(std::max<size_t>(1, l2_budget / (2 * img_bytes)));
+    group = std::min(group, 65535);
+    for (int b0 = 0; b0 < batch; b0 += group) {
+        const int nb = std::min(group, batch - b0);
+        uint8_t* img = d_img + static_cast<size_t>(b0) * img_bytes;
+        uint8_t* scr = d_scratch + static_cast<size_t>(b0) * img_bytes;
+        for (int p = 0; p < passes; ++p) {
+            boxblur_h_kernel<<<dim3(h, nb), 256, smem_h, st>>>(img, scr, w, h, channels, r, dk, img_bytes);
+            CU_TRY(cudaGetLastError());
+            if (vec)
+                boxblur_v_kernel<4><<<dim3(cdiv(pitch / 4, 128), cdiv(h, seg), nb), 128, 0, st>>>(scr, img, pitch, h, r, dk, seg, img_bytes);
+            else
+                boxblur_v_kernel<1><<<dim3(cdiv(pitch, 128), cdiv(h, seg), nb), 128, 0, st>>>(scr, img, pitch, h, r, dk, seg, img_bytes);
+            CU_TRY(cudaGetLastError());
+            g_launches += 2;
+        }
+    }
+    return BLUR_B200_OK;
+}
+
+int blur_b200_fastboxblur(uint8_t* h_img, int w, int h, int channels, int ksize, int passes)
+{
+    if (!h_img || w < 1 || h < 1 || channels < 1) return BLUR_B200_EINVAL;
+    const size_t nbytes = static_cast<size_t>(w) * h * channels;
+    uint8_t *d_img = nullptr, *d_scr = nullptr;
+    CU_TRY(cudaMalloc(&d_img, nbytes));
+    if (cudaMalloc(&d_scr, nbytes) != cudaSuccess) { cudaFree(d_img); g_cuda_err = "cudaMalloc scratch"; return BLUR_B200_ECUDA; }
+    int rc = BLUR_B200_OK;
+    if (cudaMemcpy(d_img, h_img, nbytes, cudaMemcpyHostToDevice) != cudaSuccess) rc = BLUR_B200_ECUDA;
+    if (!rc) rc = blur_b200_fastboxblur_device(d_img, w, h, channels, ksize, passes, 1, d_scr, nullptr);
+    if (!rc && cudaMemcpy(h_img, d_img, nbytes, cudaMemcpyDeviceToHost) != cudaSuccess) rc = BLUR_B200_ECUDA;
+    cudaFree(d_img); cudaFree(d_scr);
+    return rc;
+}
+
+// ---- layout utilities
+
+int blur_b200_reflect_101_u8(const uint8_t* d_in, uint8_t* d_out, int top, int bottom, int left, int right,
+                             const int original_size[2], int channels, void* stream)
+{
+    if (!d_in || !d_out || !original_size || channels < 1 || top < 0 || bottom < 0 || left < 0 || right < 0)
+        return BLUR_B200_EINVAL;
+    const int rows = original_size[0], cols = original_size[1];
+    if (rows < 1 || cols < 1) return BLUR_B200_EINVAL;
+    top = std::min(top, rows - 1); bottom = std::min(bottom, rows - 1);      // Utils.hpp:217-220
+    left = std::min(left, cols - 1); right = std::min(right, cols - 1);
+    const int prow = rows + top + bottom, pcolb = (cols + left + right) * channels;
+    reflect101_u8_kernel<<<dim3(cdiv(pcolb, 256), prow), 256, 0, static_cast<cudaStream_t>(stream)>>>(
+        d_in, d_out, rows, cols, channels, top, bottom, left, right);
+    CU_TRY(cudaGetLastError());
+    ++g_launches;
+    return BLUR_B200_OK;
+}
+
+int blur_b200_deinterleave_u8_f32(const uint8_t* d_in, float* d_b, float* d_g, float* d_r, uint32_t total, void* stream)
+{
+    if (!d_in || !d_b || !d_g || !d_r) return BLUR_B200_EINVAL;
+    if (!total) return BLUR_B200_OK;
+    deinterleave_u8_f32_kernel<<<cdiv(static_cast<int>(total), 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(d_in, d_b, d_g, d_r, total);
+    CU_TRY(cudaGetLastError());
+    ++g_launches;
+    return BLUR_B200_OK;
+}
+
+int blur_b200_interleave_f32_u8(const float* d_b, const float* d_g, const float* d_r, uint8_t* d_out, uint32_t total, void* stream)
+{
+    if (!d_out || !d_b || !d_g || !d_r) return BLUR_B200_EINVAL;
+    if (!total) return BLUR_B200_OK;
+    interleave_f32_u8_kernel<<<cdiv(static_cast<int>(total), 256), 256, 0, static_cast<cudaStream_t>(stream)>>>(d_b, d_g, d_r, d_out, total);
+    CU_TRY(cudaGetLastError());
+    ++g_launches;
+    return BLUR_B200_OK;
+}
+
+int blur_b200_flip_block_f32(const float* d_in, float* d_out, int w, int h, void* stream)
+{
+    if (!d_in || !d_out || w < 1 || h < 1) return BLUR_B200_EINVAL;
+    transpose_f32_kernel<<<dim3(cdiv(w, 32), cdiv(h, 32)), dim3(32, 8), 0, static_cast<cudaStream_t>(stream)>>>(d_in, d_out, w, h);
+    CU_TRY(cudaGetLastError());
+    ++g_launches;
+    return BLUR_B200_OK;
+}
+
+int blur_b200_reflect_101_u8_host(const uint8_t* h_in, uint8_t* h_out, int top, int bottom, int left, int right,
+                                  const int original_size[2], int channels)
+{
+    if (!h_in || !h_out || !original_size || channels < 1 || top < 0 || bottom < 0 || left < 0 || right < 0)
+        return BLUR_B200_EINVAL;
+    const int rows = original_size[0], cols = original_size[1];
+    if (rows < 1 || cols < 1) return BLUR_B200_EINVAL;
+    const int t = std::min(top, rows - 1), b = std::min(bottom, rows - 1);
+    const int l = std::min(left, cols - 1), r = std::min(right, cols - 1);
+    const size_t nin = static_cast<size_t>(rows) * cols * channels;
+    const size_t nout = static_cast<size_t>(rows + t + b) * (cols + l + r) * channels;
+    uint8_t *d_in = nullptr, *d_out = nullptr;
+    CU_TRY(cudaMalloc(&d_in, nin));
+    if (cudaMalloc(&d_out, nout) != cudaSuccess) { cudaFree(d_in); g_cuda_err = "cudaMalloc"; return BLUR_B200_ECUDA; }
+    int rc = BLUR_B200_OK;
+    if (cudaMemcpy(d_in, h_in, nin, cudaMemcpyHostToDevice) != cudaSuccess) rc = BLUR_B200_ECUDA;
+    if (!rc) rc = blur_b200_reflect_101_u8(d_in, d_out, top, bottom, left, right, original_size, channels, nullptr);
+    if (!rc && cudaMemcpy(h_out, d_out, nout, cudaMemcpyDeviceToHost) != cudaSuccess) rc = BLUR_B200_ECUDA;
+    cudaFree(d_in); cudaFree(d_out);
+    return rc;
+}
+
+uint64_t blur_b200_kernel_launches(void) { return g_launches.load(); }
+void blur_b200_count_launches(uint64_t n) { g_launches += n; }
+
+}  // extern "C"

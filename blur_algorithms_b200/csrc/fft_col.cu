@@ -1,0 +1,18 @@
+// fft_col.cu — column-pass instantiation: Q -> uint8 planar transposed U (Source.cpp:546-567).
+#include "fft_kernels.cuh"
+#include "fft_launch.hpp"
+
+namespace blurb200 {
+cudaError_t launch_fft_col(const FftGeom& g, const ColIO& io, const float2* tw, const float* kt, int batch,
+                           int grid, int threads, size_t smem, cudaStream_t stream)
+{
+    static size_t configured = 0;
+    if (smem > configured) {
+        cudaError_t e = cudaFuncSetAttribute(fft_conv_kernel<ColIO>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        configured = smem;
+    }
+    fft_conv_kernel<ColIO><<<grid, threads, smem, stream>>>(g, io, tw, kt, batch);
+    return cudaGetLastError();
+}
+}  // namespace blurb200

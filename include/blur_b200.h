@@ -1,0 +1,143 @@
+/*
+ * blur_b200.h — C ABI of the B200-native drop-in for the hot path of
+ * michelerenzullo/Blur_algorithms (reference commit 2f873a4e).
+ *
+ * Plain pointers and sizes only.  Every entry point names the reference interface it
+ * replaces (file:line into the reference tree).  All functions return 0 on success or a
+ * BLUR_B200_E* code; blur_b200_strerror() explains it.  There is no CPU fallback: without a
+ * CUDA device every compute entry point returns BLUR_B200_ECUDA.
+ *
+ * Pointer naming: h_* = host memory, d_* = device memory on the plan's device.
+ * `stream` is a cudaStream_t passed as void* (NULL = default stream).
+ */
+#ifndef BLUR_B200_H
+#define BLUR_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+enum {
+    BLUR_B200_OK = 0,
+    BLUR_B200_EINVAL = 1,      /* bad argument (null pointer, non-positive size, ...) */
+    BLUR_B200_EPAD = 2,        /* kernel half-width exceeds min(rows,cols)-1: the reference would
+                                  read out of bounds (README.md:33-38); we refuse instead */
+    BLUR_B200_ESIZE = 3,       /* FFT length not plannable / exceeds shared memory (N > 28160) */
+    BLUR_B200_ECUDA = 4,       /* CUDA runtime error (see blur_b200_last_cuda_error) */
+    BLUR_B200_ENOMEM = 5
+};
+
+/* nyquist_mode for the Gaussian paths */
+enum {
+    BLUR_B200_NYQUIST_EXACT = 0,  /* every bin multiplied by its own kernel gain:
+                                     pocketfft_1D (Source.cpp:362,378) and pocketfft_2D (:258) */
+    BLUR_B200_NYQUIST_PFFFT = 1   /* pffft_sorted_optimized_convolution (Source.cpp:414-427):
+                                     bin N/2 multiplied by the kernel's DC gain */
+};
+
+const char *blur_b200_strerror(int code);
+const char *blur_b200_last_cuda_error(void);
+
+/* ---- sizing helpers (host, exact integer semantics of the reference) --------------------- */
+int blur_b200_is_valid_size(int n);                         /* isValidSize,          Utils.hpp:141-148 */
+int blur_b200_nearest_transform_size(int n);                /* nearestTransformSize, Utils.hpp:150-157 */
+int blur_b200_gaussian_window(double sigma, int max_width); /* gaussian_window,      Source.cpp:60-73  */
+/* getGaussian, Source.cpp:75-102.  kernel must hold max(width, fft_length) floats; width 0 =
+ * gaussian_window(sigma). */
+int blur_b200_get_gaussian(float *kernel, double sigma, int width, int fft_length);
+
+/* Derived sizes of the 1-D tile path (Source.cpp:434-457): out[0]=kSize out[1]=pad
+ * out[2]=sizes[0] (column FFT length) out[3]=sizes[1] (row FFT length). */
+int blur_b200_gauss_geometry(int rows, int cols, double sigma, int out[4]);
+
+/* ---- Gaussian blur, 1-D tile path (pffft_ Source.cpp:429-570, pocketfft_1D :280-392) ------ */
+
+typedef struct blur_b200_plan blur_b200_plan;
+
+/* Plan = cached twiddles + separable kernel spectra (row and column) + device workspaces for a
+ * (rows, cols, sigma, nyquist_mode) problem on `device`.  Replaces the per-call
+ * pffft_new_setup / getGaussian / kernel FFT of Source.cpp:465-503. */
+int blur_b200_gauss_plan_create(blur_b200_plan **plan, int rows, int cols, double sigma,
+                                int nyquist_mode, int device);
+
+/* Sharded plan for one rank of a row-stripe x column-stripe decomposition of a single image
+ * (SURVEY.md §8e).  The image is rows x cols; this rank owns image rows
+ * [rank*stripe_rows, min(rows, (rank+1)*stripe_rows)) in the row pass and column pairs
+ * [rank*cpp, (rank+1)*cpp) in the column pass, where stripe_rows = even_ceil(rows/nranks) and
+ * cpp = ceil(ceil(cols/2)/nranks) are reported by blur_b200_gauss_plan_info. */
+int blur_b200_gauss_plan_create_sharded(blur_b200_plan **plan, int rows, int cols, double sigma,
+                                        int nyquist_mode, int device, int rank, int nranks);
+void blur_b200_gauss_plan_destroy(blur_b200_plan *plan);
+
+/* info[0]=kSize [1]=pad [2]=n_col [3]=n_row [4]=stripe_rows [5]=cpp (column pairs per rank)
+ * [6]=rank's first row [7]=rank's valid rows [8]=floats per (stripe,part) block of Q
+ * [9]=kernel launches per run [10]=threads row kernel [11]=threads col kernel
+ * [12]=batch row [13]=batch col [14]=smem row [15]=smem col */
+int blur_b200_gauss_plan_info(const blur_b200_plan *plan, int64_t info[16]);
+
+/* Whole blur, device resident: d_in and d_out are uint8 [rows][cols][3]; may alias (in place,
+ * like image.data in the reference). */
+int blur_b200_gauss_run_device(blur_b200_plan *plan, const uint8_t *d_in, uint8_t *d_out, void *stream);
+
+/* Whole blur on host buffers (pinned or pageable); H2D + kernels + D2H.  In place allowed. */
+int blur_b200_gauss_run_host(blur_b200_plan *plan, const uint8_t *h_in, uint8_t *h_out);
+
+/* One-shot drop-in for `pffft_(image, sigma)` / `pocketfft_1D` / `pocketfft_2D` acting on
+ * image.data in place (Source.cpp:429,280,143): creates a plan, runs, destroys. */
+int blur_b200_gauss_u8c3(uint8_t *h_bgr, int rows, int cols, double sigma, int nyquist_mode);
+
+/* Pieces of the sharded pipeline (single-GPU plans accept them too, with nranks = 1):
+ *   row pass : d_in_stripe = this rank's rows of the image (uint8 [valid rows][cols][3])
+ *              d_q         = float [nranks][3][cpp][stripe_rows][2]  (block p goes to rank p)
+ *   col pass : d_q_chunks  = float [nranks][3][cpp][stripe_rows][2]  (block s came from rank s)
+ *              d_out_cols  = uint8 [rows][2*cpp][3]  this rank's column stripe of the result */
+int blur_b200_gauss_row_pass(blur_b200_plan *plan, const uint8_t *d_in_stripe, float *d_q, void *stream);
+int blur_b200_gauss_col_pass(blur_b200_plan *plan, const float *d_q_chunks, uint8_t *d_out_cols, void *stream);
+
+/* Parity hook: the float32 row-pass result (`resf` of Source.cpp:536) as planar [3][rows][cols]. */
+int blur_b200_gauss_rowpass_f32(blur_b200_plan *plan, const uint8_t *d_in, float *d_planar, void *stream);
+
+/* ---- FastBoxBlur (fastboxblur(in,w,h,channels,ksize,passes), call site Source.cpp:587) ------
+ * Declared semantics (upstream source absent): r=(ksize-1)/2, k=2r+1,
+ * reflect-101, horizontal then vertical sliding sums, uint8 after each 1-D pass with
+ * (2*acc+k)/(2k), `passes` repeats, in place.  `batch` images back to back. */
+int blur_b200_fastboxblur_device(uint8_t *d_img, int w, int h, int channels, int ksize, int passes,
+                                 int batch, uint8_t *d_scratch /* batch*w*h*channels bytes */, void *stream);
+int blur_b200_fastboxblur(uint8_t *h_img, int w, int h, int channels, int ksize, int passes);
+
+/* ---- layout utilities (device pointers) ------------------------------------------------------ */
+/* Reflect_101<uint8_t,C>, Utils.hpp:212-243.  original_size = {rows, cols}.  Pads are clamped to
+ * dim-1 like the reference; d_out must hold (rows+top+bottom)*(cols+left+right)*channels bytes
+ * computed with the CLAMPED pads. */
+int blur_b200_reflect_101_u8(const uint8_t *d_in, uint8_t *d_out, int top, int bottom, int left, int right,
+                             const int original_size[2], int channels, void *stream);
+/* same on host buffers (H2D + kernel + D2H): the signature of the reference template */
+int blur_b200_reflect_101_u8_host(const uint8_t *h_in, uint8_t *h_out, int top, int bottom, int left, int right,
+                                  const int original_size[2], int channels);
+/* deinterleave_BGR<uint8_t,float> / interleave_BGR<uint8_t,float>, Utils.hpp:159-210 */
+int blur_b200_deinterleave_u8_f32(const uint8_t *d_in, float *d_b, float *d_g, float *d_r, uint32_t total, void *stream);
+int blur_b200_interleave_f32_u8(const float *d_b, const float *d_g, const float *d_r, uint8_t *d_out, uint32_t total, void *stream);
+/* flip_block<float,1>(in,out,w,h): in is h x w, out is w x h (call sites Source.cpp:540,562) */
+int blur_b200_flip_block_f32(const float *d_in, float *d_out, int w, int h, void *stream);
+
+/* ---- DFT_image spectrum path (pocketfft_2D with #define DFT_image, Source.cpp:240-252) ------- */
+/* d_in uint8 [rows][cols][3]; d_out uint8 [rows][cols][3] spectrum image; optional d_spec_f32
+ * float planar [3][H][W] of the padded size (H,W returned in padded[2]). nsmooth selects the
+ * padding exactly as pocketfft_2D does. */
+int blur_b200_dft_image_device(const uint8_t *d_in, uint8_t *d_out, int rows, int cols, double nsmooth,
+                               float *d_spec_f32, int padded[2], void *stream);
+int blur_b200_dft_image_host(const uint8_t *h_in, uint8_t *h_out, int rows, int cols, double nsmooth,
+                             float *h_spec_f32, int padded[2]);
+/* padded = {sizes[0], sizes[1]}, border = {top, bottom, left, right} of Source.cpp:160-176 */
+int blur_b200_dft_image_sizes(int rows, int cols, double nsmooth, int padded[2], int border[4]);
+
+/* Number of kernels this library has launched in this process (bench.py reports it). */
+uint64_t blur_b200_kernel_launches(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,211 @@
+// tests/emul/emulate.cpp — TEST INFRASTRUCTURE (never linked into the product library).
+//
+// Executes the device code of blur_algorithms_b200/csrc (fft_core.cuh, blur_io.cuh,
+// fft_plan.hpp — the very same host/device functions the CUDA kernels call) on the CPU, one
+// "thread" after another, with the kernel's barrier structure turned into sequential phases.
+// Lets the `-m "not gpu"` suite check the FFT decomposition, scrambled multiply, tile placement
+// and HBM layouts against the oracle without a GPU.
+#include <cstdio>
+#include <vector>
+#include "../../blur_algorithms_b200/csrc/fft_plan.hpp"
+#include "../../blur_algorithms_b200/csrc/blur_io.cuh"
+#include "../../blur_algorithms_b200/csrc/fft_dispatch.cuh"
+
+using namespace blurb200;
+
+template <class IO>
+static void run_units(const FftGeom& g, const IO& io, const std::vector<float2>& tw, const std::vector<float>& kt)
+{
+#pragma omp parallel
+    {
+        std::vector<float2> smem(static_cast<size_t>(g.slots));
+        float2* s = smem.data();
+#pragma omp for schedule(dynamic, 4)
+        for (int unit = 0; unit < io.nunits; ++unit) {
+#define F0(R) for (int u = 0; u < g.W[0]; ++u) fwd_pass<R, true>(s, g, 0, u, tw.data(), io, unit)
+            BLUR_RADIX_SWITCH(g.radix[0], F0)
+#undef F0
+            for (int p = 1; p < g.npass - 1; ++p) {
+#define F1(R) for (int u = 0; u < g.W[p]; ++u) fwd_pass<R, false>(s, g, p, u, tw.data(), io, unit)
+                BLUR_RADIX_SWITCH(g.radix[p], F1)
+#undef F1
+            }
+            for (int u = 0; u < g.N / kLastRadix; ++u) mid_pass(s, g, u, kt.data());
+            for (int p = g.npass - 2; p >= 1; --p) {
+#define F2(R) for (int u = 0; u < g.W[p]; ++u) inv_pass<R, false>(s, g, p, u, tw.data(), io, unit)
+                BLUR_RADIX_SWITCH(g.radix[p], F2)
+#undef F2
+            }
+#define F3(R) for (int u = 0; u < g.W[0]; ++u) inv_pass<R, true>(s, g, 0, u, tw.data(), io, unit)
+            BLUR_RADIX_SWITCH(g.radix[0], F3)
+#undef F3
+        }
+    }
+}
+
+extern "C" {
+
+// Gaussian 1-D tile path on the CPU through the device code.  nparts > 1 exercises the
+// multi-GPU Q layout (row stripes x column-pair parts) inside one process.
+// rowpass_planar (optional): float [3][rows][cols].  Returns 0 on success.
+int emul_gauss(const uint8_t* in, uint8_t* out, int rows, int cols, double sigma, int nyquist_mode,
+               int nparts, float* rowpass_planar, int* radices_row, int* radices_col)
+{
+    const GaussGeometry gg = gauss_geometry(rows, cols, sigma);
+    if (gg.pad < 0 || gg.pad > rows - 1 || gg.pad > cols - 1) return 2;
+    FftGeom grow, gcol;
+    if (!make_geom(gg.n_row, grow) || !make_geom(gg.n_col, gcol)) return 3;
+    if (radices_row) for (int i = 0; i < kMaxPass; ++i) radices_row[i] = i < grow.npass ? grow.radix[i] : 0;
+    if (radices_col) for (int i = 0; i < kMaxPass; ++i) radices_col[i] = i < gcol.npass ? gcol.radix[i] : 0;
+    std::vector<float2> tw_row, tw_col;
+    make_twiddles(grow.N, tw_row);
+    make_twiddles(gcol.N, tw_col);
+    std::vector<double> K;
+    std::vector<float> kt_row, kt_col;
+    kernel_spectrum(sigma, gg.ksize, grow.N, K);
+    make_kt(grow, K, nyquist_mode, kt_row);
+    kernel_spectrum(sigma, gg.ksize, gcol.N, K);
+    make_kt(gcol, K, nyquist_mode, kt_col);
+
+    // "GPUs": stripe s owns rows [s*srows, ...), part p owns column pairs [p*cpp, ...)
+    const int P = nparts;
+    const int cp_total = (cols + 1) / 2;
+    const int cpp = (cp_total + P - 1) / P;
+    int srows = (rows + P - 1) / P;
+    srows += srows & 1;                                   // stripes start on even rows
+    const size_t part_elems = static_cast<size_t>(3) * cpp * srows * 2;   // floats per (stripe, part)
+    std::vector<std::vector<float>> Q(P, std::vector<float>(part_elems * P, 0.f));   // Q[stripe][part][...]
+    for (int s = 0; s < P; ++s) {
+        const int r0 = s * srows, nr = std::max(0, std::min(srows, rows - r0));
+        if (nr <= 0) continue;
+        RowIO io{};
+        io.in = in + static_cast<size_t>(r0) * cols * 3;
+        io.q = Q[s].data();
+        io.rows = nr; io.cols = cols; io.pad = gg.pad; io.N = grow.N;
+        io.qrows = srows; io.cpp = cpp;
+        io.nunits = ((nr + 3) / 4) * 6;
+        run_units(grow, io, tw_row, kt_row);
+    }
+    if (rowpass_planar) {
+        for (int s = 0; s < P; ++s)
+            for (int ch = 0; ch < 3; ++ch)
+                for (int r = s * srows; r < std::min(rows, (s + 1) * srows); ++r)
+                    for (int x = 0; x < cols; ++x) {
+                        const int cp = x >> 1, part = cp / cpp, cpl = cp - part * cpp;
+                        rowpass_planar[(static_cast<size_t>(ch) * rows + r) * cols + x] =
+                            Q[s][((static_cast<size_t>(part * 3 + ch) * cpp + cpl) * srows + (r - s * srows)) * 2 + (x & 1)];
+                    }
+    }
+    // "all-to-all": part p gathers block p of every stripe -> chunks [stripe][3][cpp][srows][2]
+    for (int p = 0; p < P; ++p) {
+        std::vector<float> recv(part_elems * P);
+        for (int s = 0; s < P; ++s)
+            std::copy(Q[s].begin() + part_elems * p, Q[s].begin() + part_elems * (p + 1), recv.begin() + part_elems * s);
+        const int cp0 = p * cpp, ncp = std::max(0, std::min(cpp, cp_total - cp0));
+        if (ncp <= 0) continue;
+        std::vector<uint8_t> U(static_cast<size_t>(3) * 2 * cpp * rows);
+        ColIO io{};
+        io.q = reinterpret_cast<const float2*>(recv.data());
+        io.chunk_stride = part_elems / 2;
+        io.chunk_rows = srows;
+        io.u = U.data();
+        io.rows = rows; io.ncp = cpp; io.valid_ncp = ncp; io.ucols = 2 * cpp; io.pad = gg.pad; io.N = gcol.N;
+        io.nunits = 3 * cpp;
+        run_units(gcol, io, tw_col, kt_col);
+        for (int ch = 0; ch < 3; ++ch)
+            for (int c = 0; c < 2 * ncp; ++c) {
+                const int x = 2 * cp0 + c;
+                if (x >= cols) continue;
+                for (int r = 0; r < rows; ++r)
+                    out[(static_cast<size_t>(r) * cols + x) * 3 + ch] = U[(static_cast<size_t>(ch) * 2 * cpp + c) * rows + r];
+            }
+    }
+    return 0;
+}
+
+// Per-rank pieces with the exact buffer contract of blur_b200_gauss_row_pass / _col_pass, so the
+// CPU (gloo) tests can run blur_algorithms_b200/dist.py without a GPU.
+int emul_row_pass(const uint8_t* in_stripe, float* q, int rows, int cols, double sigma, int nyquist_mode,
+                  int rank, int nranks)
+{
+    const GaussGeometry gg = gauss_geometry(rows, cols, sigma);
+    FftGeom grow;
+    if (!make_geom(gg.n_row, grow)) return 3;
+    std::vector<float2> tw; make_twiddles(grow.N, tw);
+    std::vector<double> K; std::vector<float> kt;
+    kernel_spectrum(sigma, gg.ksize, grow.N, K); make_kt(grow, K, nyquist_mode, kt);
+    const int cp_total = (cols + 1) / 2, cpp = (cp_total + nranks - 1) / nranks;
+    int srows = (rows + nranks - 1) / nranks; srows += srows & 1;
+    const int r0 = rank * srows, nr = std::max(0, std::min(srows, rows - r0));
+    if (nr <= 0) return 0;
+    RowIO io{};
+    io.in = in_stripe; io.q = q; io.rows = nr; io.cols = cols; io.pad = gg.pad; io.N = grow.N;
+    io.qrows = srows; io.cpp = cpp; io.nunits = ((nr + 3) / 4) * 6;
+    run_units(grow, io, tw, kt);
+    return 0;
+}
+
+int emul_col_pass(const float* q_chunks, uint8_t* out_cols, int rows, int cols, double sigma, int nyquist_mode,
+                  int rank, int nranks)
+{
+    const GaussGeometry gg = gauss_geometry(rows, cols, sigma);
+    FftGeom gcol;
+    if (!make_geom(gg.n_col, gcol)) return 3;
+    std::vector<float2> tw; make_twiddles(gcol.N, tw);
+    std::vector<double> K; std::vector<float> kt;
+    kernel_spectrum(sigma, gg.ksize, gcol.N, K); make_kt(gcol, K, nyquist_mode, kt);
+    const int cp_total = (cols + 1) / 2, cpp = (cp_total + nranks - 1) / nranks;
+    int srows = (rows + nranks - 1) / nranks; srows += srows & 1;
+    const size_t part_elems = static_cast<size_t>(3) * cpp * srows * 2;
+    std::vector<uint8_t> U(static_cast<size_t>(3) * 2 * cpp * rows);
+    ColIO io{};
+    io.q = reinterpret_cast<const float2*>(q_chunks);
+    io.chunk_stride = part_elems / 2; io.chunk_rows = srows; io.u = U.data();
+    io.rows = rows; io.ncp = cpp; io.valid_ncp = std::max(0, std::min(cpp, cp_total - rank * cpp));
+    io.ucols = 2 * cpp; io.pad = gg.pad; io.N = gcol.N; io.nunits = 3 * cpp;
+    run_units(gcol, io, tw, kt);
+    for (int r = 0; r < rows; ++r)
+        for (int c = 0; c < 2 * cpp; ++c)
+            for (int ch = 0; ch < 3; ++ch)
+                out_cols[(static_cast<size_t>(r) * 2 * cpp + c) * 3 + ch] = U[(static_cast<size_t>(ch) * 2 * cpp + c) * rows + r];
+    return 0;
+}
+
+// raw complex round trip through the passes for one length (no kernel): out = ifft(fft(in) * 1/N)
+int emul_fft_roundtrip(int N, const float* in_re, const float* in_im, float* out_re, float* out_im,
+                       float* spec_re, float* spec_im)
+{
+    FftGeom g;
+    if (!make_geom(N, g)) return 3;
+    std::vector<float2> tw;
+    make_twiddles(N, tw);
+    struct IO {
+        const float *ir, *ii; float *orr, *oi; int nunits;
+        struct Ctx {};
+        Ctx begin(int) const { return Ctx(); }
+        void load(const Ctx&, int n, float& re, float& im) const { re = ir[n]; im = ii[n]; }
+        void store(const Ctx&, int n, float re, float im) const { orr[n] = re; oi[n] = im; }
+    } io{in_re, in_im, out_re, out_im, 1};
+    std::vector<float> kt(static_cast<size_t>(N), 1.f / N);
+    run_units(g, io, tw, kt);
+    if (spec_re) {
+        // forward only, unscrambled, for checking against numpy.fft
+        std::vector<float2> s(static_cast<size_t>(g.slots));
+#define F0(R) for (int u = 0; u < g.W[0]; ++u) fwd_pass<R, true>(s.data(), g, 0, u, tw.data(), io, 0)
+        BLUR_RADIX_SWITCH(g.radix[0], F0)
+#undef F0
+        for (int p = 1; p < g.npass - 1; ++p) {
+#define F1(R) for (int u = 0; u < g.W[p]; ++u) fwd_pass<R, false>(s.data(), g, p, u, tw.data(), io, 0)
+            BLUR_RADIX_SWITCH(g.radix[p], F1)
+#undef F1
+        }
+        for (int u = 0; u < N / 32; ++u) {
+            float xr[32], xi[32];
+            for (int j = 0; j < 32; ++j) { xr[j] = s[u * 33 + j].x; xi[j] = s[u * 33 + j].y; }
+            Dft<32, false>::run(xr, xi);
+            for (int q = 0; q < 32; ++q) { int k = scrambled_freq(g, 32 * u + q); spec_re[k] = xr[q]; spec_im[k] = xi[q]; }
+        }
+    }
+    return 0;
+}
+}

@@ -1,0 +1,300 @@
+"""GPU (-m gpu): the CUDA path, called through the C ABI (blur_algorithms_b200 -> ctypes ->
+libblur_b200.so), against the CPU oracle on the same seeded inputs, against the committed golden
+fixtures, and — at BASELINE.json's full sizes — through size-independent properties.
+
+Tolerances (BASELINE.json north_star): uint8 output within +-1 LSB of the reference path;
+float32 intermediates within 1e-5 relative (relative to the 0..255 data range: <= 255e-5);
+FastBoxBlur bit-exact.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from util import GOLDEN, GOLDEN_BOX_CASES, GOLDEN_CASES, box_numpy, golden_outputs, synth
+
+pytestmark = pytest.mark.gpu
+
+F32_TOL = 255 * 1e-5
+
+
+@pytest.fixture(scope="module")
+def bb():
+    import blur_algorithms_b200 as m
+    return m
+
+
+@pytest.fixture(scope="module")
+def torch():
+    import torch as t
+    assert t.cuda.is_available()
+    return t
+
+
+def lsb(a, b):
+    return int(np.abs(a.astype(np.int32) - b.astype(np.int32)).max())
+
+
+# ---------------------------------------------------------------- Gaussian, small sizes vs oracle
+
+@pytest.mark.parametrize("rows,cols,sigma", [
+    (64, 96, 2.0), (100, 75, 3.0), (135, 241, 6.0), (240, 320, 5.0), (467, 700, 7.5), (33, 40, 1.0), (32, 32, 0.5),
+    (1080, 1920, 5.0),      # BASELINE config 1
+])
+def test_gauss_vs_oracle(bb, oracle, rows, cols, sigma):
+    img = synth("noise", rows, cols, 3)
+    for fn, mode in ((bb.pocketfft_1D, 0), (bb.pffft_, 1)):
+        ref = oracle.gauss_blur_1d(img, sigma, mode)
+        out = img.copy()
+        fn(out, sigma)
+        assert lsb(out, ref) <= 1, (rows, cols, sigma, mode)
+        assert (out != ref).mean() < 1e-3
+    out = img.copy()
+    bb.pocketfft_2D(out, sigma)
+    assert lsb(out, oracle.gauss_blur_2d(img, sigma)) <= 1
+
+
+@pytest.mark.parametrize("kind", ["const", "impulse", "stripes", "ramp"])
+def test_gauss_edge_inputs(bb, oracle, kind):
+    img = synth(kind, 96, 128)
+    for fn, mode in ((bb.pocketfft_1D, 0), (bb.pffft_, 1)):
+        out = img.copy()
+        fn(out, 2.5)
+        assert lsb(out, oracle.gauss_blur_1d(img, 2.5, mode)) <= 1
+    if kind == "const":
+        assert np.all(out == 200)
+
+
+def test_gauss_golden_reference_outputs(bb):
+    gold = golden_outputs()
+    for kind, rows, cols, sigma in GOLDEN_CASES:
+        img = synth(kind, rows, cols)
+        key = f"{kind}_{rows}x{cols}_s{sigma}"
+        for fn, suffix in ((bb.pocketfft_1D, "_pocketfft1d"), (bb.pffft_, "_pffft"), (bb.pocketfft_2D, "_pocketfft2d")):
+            out = img.copy()
+            fn(out, sigma)
+            assert lsb(out, gold[key + suffix]) <= 1, key + suffix
+
+
+def test_gauss_float32_intermediate(bb, oracle, torch):
+    for rows, cols, sigma, mode in [(240, 320, 5.0, 0), (135, 241, 6.0, 1), (1080, 1920, 5.0, 0)]:
+        img = synth("noise", rows, cols, 4)
+        _, rp, _ = oracle.gauss_blur_1d(img, sigma, mode, want_f32=True)
+        plan = bb.GaussPlan(rows, cols, sigma, mode)
+        d_in = torch.from_numpy(img).cuda()
+        d_pl = torch.empty((3, rows, cols), dtype=torch.float32, device="cuda")
+        plan.rowpass_f32(d_in, d_pl)
+        torch.cuda.synchronize()
+        assert np.abs(d_pl.cpu().numpy() - rp).max() <= F32_TOL
+        plan.close()
+
+
+def test_gauss_device_entry_in_place_and_repeatable(bb, oracle, torch):
+    img = synth("noise", 300, 200, 8)
+    plan = bb.GaussPlan(300, 200, 4.0, 0)
+    d = torch.from_numpy(img).cuda()
+    o1 = torch.empty_like(d)
+    plan.run(d, o1)
+    plan.run(d)           # in place
+    torch.cuda.synchronize()
+    assert torch.equal(d, o1)
+    assert lsb(d.cpu().numpy(), oracle.gauss_blur_1d(img, 4.0, 0)) <= 1
+    h = img.copy()
+    plan.run_host(h)
+    assert np.array_equal(h, o1.cpu().numpy())
+    plan.close()
+
+
+def test_gauss_errors(bb):
+    with pytest.raises(bb.BlurB200Error) as e:
+        bb.pffft_(synth("noise", 16, 400), 50.0)      # pad 165 > rows-1: reference would read OOB
+    assert e.value.code == 2
+    with pytest.raises(bb.BlurB200Error):
+        bb.GaussPlan(64, 64, -1.0)
+
+
+def test_gauss_sharded_emulated_on_one_gpu(bb, torch):
+    """P ranks' plans executed one after another on one GPU with the all-to-all done by copies:
+    bit-identical to the single-plan result (SURVEY.md §4 multi-GPU test plan)."""
+    for rows, cols, sigma, mode, P in [(135, 241, 6.0, 1, 3), (240, 320, 5.0, 0, 2), (256, 256, 3.0, 0, 8)]:
+        img = synth("noise", rows, cols, 6)
+        single = torch.from_numpy(img).cuda()
+        p1 = bb.GaussPlan(rows, cols, sigma, mode)
+        p1.run(single)
+        plans = [bb.GaussPlan(rows, cols, sigma, mode, rank=r, nranks=P) for r in range(P)]
+        bf = plans[0].info["block_floats"]
+        send = [torch.zeros(P * bf, dtype=torch.float32, device="cuda") for _ in range(P)]
+        d_img = torch.from_numpy(img).cuda()
+        for r, pl in enumerate(plans):
+            if pl.info["valid_rows"] > 0:
+                pl.row_pass(d_img[pl.info["row0"]:pl.info["row0"] + pl.info["valid_rows"]].contiguous(), send[r])
+        outs = []
+        for r, pl in enumerate(plans):
+            recv = torch.cat([send[s][r * bf:(r + 1) * bf] for s in range(P)])
+            oc = torch.zeros((rows, 2 * pl.info["cpp"], 3), dtype=torch.uint8, device="cuda")
+            pl.col_pass(recv, oc)
+            outs.append(oc)
+        torch.cuda.synchronize()
+        full = torch.cat(outs, 1)[:, :cols]
+        assert torch.equal(full, single), (rows, cols, P)
+        for pl in plans + [p1]:
+            pl.close()
+
+
+# ---------------------------------------------------------------- full-size properties
+
+def _sample_exact(oracle, img, sigma, pts):
+    """float64 direct separable convolution at a few sample pixels (reflect-101)."""
+    rows, cols = img.shape[:2]
+    k = oracle.gaussian_window(sigma, max(rows, cols))
+    pad = (k - 1) // 2
+    g = oracle.get_gaussian(sigma, k, 0).astype(np.float64)
+    idx = np.arange(-pad, pad + 1)
+
+    def refl(i, L):
+        i = np.abs(i)
+        return np.where(i >= L, 2 * (L - 1) - i, i)
+    out = []
+    for (r, c) in pts:
+        rr, cc = refl(r + idx, rows), refl(c + idx, cols)
+        patch = img[np.ix_(rr, cc)].astype(np.float64)          # [k, k, 3]
+        out.append(np.einsum("i,j,ijc->c", g, g, patch))
+    return np.array(out)
+
+
+@pytest.mark.parametrize("rows,cols,sigma", [(2160, 3840, 25.0), (16384, 16384, 50.0)])   # BASELINE configs 2, 3
+def test_gauss_full_size_properties(bb, oracle, torch, rows, cols, sigma):
+    plan = bb.GaussPlan(rows, cols, sigma, 0)
+    # constant image stays constant (DC gain exactly 1 after rounding)
+    d = torch.full((rows, cols, 3), 77, dtype=torch.uint8, device="cuda")
+    plan.run(d)
+    assert int(d.min()) == 77 and int(d.max()) == 77
+    # seeded noise: sampled pixels against an exact float64 direct convolution, incl. corners/edges
+    rng = np.random.default_rng(0)
+    img = rng.integers(0, 256, (rows, cols, 3), dtype=np.uint8)
+    d = torch.from_numpy(img).cuda()
+    plan.run(d)
+    out = d.cpu().numpy()
+    pts = [(0, 0), (0, cols - 1), (rows - 1, 0), (rows - 1, cols - 1), (rows // 2, cols // 2), (1, cols // 3),
+           (rows - 2, 5), (rows // 3, cols - 1)] + [(int(rng.integers(rows)), int(rng.integers(cols))) for _ in range(24)]
+    exact = _sample_exact(oracle, img, sigma, pts)
+    got = np.array([out[r, c] for r, c in pts]).astype(np.float64)
+    assert np.abs(got - np.floor(exact + 0.5)).max() <= 1
+    # linearity / symmetry: blur(255 - x) == 255 - blur(x) within rounding
+    d2 = torch.from_numpy(255 - img).cuda()
+    plan.run(d2)
+    s = (d2.to(torch.int16) + d.to(torch.int16))
+    assert int((s - 255).abs().max()) <= 1
+    # mean is preserved by a unit-gain reflect-padded blur only approximately; check it stays close
+    assert abs(float(out.mean()) - float(img.mean())) < 0.5
+    plan.close()
+
+
+def test_gauss_4k_vs_oracle(bb, oracle):
+    """BASELINE config 2 in full against the oracle (a few seconds of CPU)."""
+    img = synth("noise", 2160, 3840, 0)
+    ref = oracle.gauss_blur_1d(img, 25.0, 0)
+    out = img.copy()
+    bb.pocketfft_1D(out, 25.0)
+    assert lsb(out, ref) <= 1 and (out != ref).mean() < 1e-3
+    ref = oracle.gauss_blur_1d(img, 25.0, 1)
+    out = img.copy()
+    bb.pffft_(out, 25.0)
+    assert lsb(out, ref) <= 1
+
+
+# ---------------------------------------------------------------- box blur (bit-exact)
+
+def test_box_bit_exact_small(bb, oracle):
+    gold = golden_outputs()
+    for kind, rows, cols, ns in GOLDEN_BOX_CASES:
+        img = synth(kind, rows, cols)
+        out = img.copy()
+        bb.Test(out, 4, ns)
+        assert np.array_equal(out, gold[f"{kind}_{rows}x{cols}_n{ns}_box"])
+        assert np.array_equal(out, oracle.fastboxblur(img, int(ns * ns), 2))
+    for ch, ks, passes, shape in [(1, 7, 1, (40, 50)), (4, 11, 3, (33, 47)), (3, 8, 2, (64, 64)), (2, 5, 1, (31, 29)), (3, 1, 2, (20, 20))]:
+        rng = np.random.default_rng(ch)
+        img = rng.integers(0, 256, shape + (ch,), dtype=np.uint8)
+        out = img.copy()
+        bb.fastboxblur(out, shape[1], shape[0], ch, ks, passes)
+        assert np.array_equal(out, box_numpy(img, ks, passes)), (ch, ks)
+    with pytest.raises(bb.BlurB200Error):
+        bb.fastboxblur(np.zeros((10, 10, 3), np.uint8), 10, 10, 3, 25, 1)
+
+
+def test_box_bit_exact_1080p_batch(bb, oracle, torch):
+    """BASELINE config 5 shape (radius 15, 2 passes), a batch of 8 images, against the oracle."""
+    imgs = np.stack([synth("noise", 1080, 1920, s) for s in range(8)])
+    d = torch.from_numpy(imgs).cuda()
+    scr = torch.empty_like(d)
+    bb.fastboxblur_device(d, 1920, 1080, 3, 31, 2, 8, scr)
+    torch.cuda.synchronize()
+    out = d.cpu().numpy()
+    for s in (0, 3, 7):
+        assert np.array_equal(out[s], oracle.fastboxblur(imgs[s], 31, 2))
+    # idempotence-like property: a constant image is a fixed point
+    c = torch.full((2, 1080, 1920, 3), 131, dtype=torch.uint8, device="cuda")
+    bb.fastboxblur_device(c, 1920, 1080, 3, 31, 2, 2, torch.empty_like(c))
+    assert int(c.min()) == 131 and int(c.max()) == 131
+
+
+# ---------------------------------------------------------------- layout utilities
+
+def test_reflect_101(bb, oracle):
+    row = np.frombuffer(b"ABCDEFG", np.uint8).reshape(1, 7)
+    assert bytes(bb.Reflect_101(row, 0, 0, 6, 6)[0]) == b"GFEDCBABCDEFGFEDCBA"
+    img = synth("noise", 37, 53, 7)
+    for pads in [(1, 2, 2, 1), (0, 0, 0, 0), (5, 7, 3, 9), (36, 36, 52, 52), (50, 50, 80, 80)]:
+        assert np.array_equal(bb.Reflect_101(img, *pads), oracle.reflect_101(img, *pads)), pads
+    g = img[..., 0].copy()
+    assert np.array_equal(bb.Reflect_101(g, 3, 4, 5, 6), oracle.reflect_101(g, 3, 4, 5, 6))
+
+
+def test_deinterleave_interleave_flip(bb, oracle, torch):
+    img = synth("noise", 50, 70, 2)
+    total = 50 * 70
+    d = torch.from_numpy(img).cuda()
+    planes = torch.empty((3, total), dtype=torch.float32, device="cuda")
+    bb.deinterleave_BGR(d, planes, total)
+    assert np.array_equal(planes.cpu().numpy(), oracle.deinterleave(img))
+    vals = torch.tensor([[0.4, 0.5, 254.6, 255.4]] * 3, dtype=torch.float32, device="cuda")
+    o = torch.empty(12, dtype=torch.uint8, device="cuda")
+    bb.interleave_BGR(vals, o, 4)
+    assert o.cpu().tolist() == [0, 0, 0, 1, 1, 1, 255, 255, 255, 255, 255, 255]
+    back = torch.empty_like(d)
+    bb.interleave_BGR(planes, back, total)
+    assert torch.equal(back, d)
+    a = torch.arange(50 * 70, dtype=torch.float32, device="cuda").reshape(50, 70)
+    t = torch.empty((70, 50), dtype=torch.float32, device="cuda")
+    bb.flip_block(a, t, 70, 50)
+    assert torch.equal(t, a.t().contiguous())
+
+
+# ---------------------------------------------------------------- DFT_image
+
+def test_dft_image_vs_oracle_and_golden(bb, oracle):
+    cv2 = pytest.importorskip("cv2")
+    im = cv2.imread(os.path.join(GOLDEN, "spectrum_in_blur200.png"), cv2.IMREAD_COLOR)
+    gold = cv2.imread(os.path.join(GOLDEN, "spectrum_out_blur200.png"), cv2.IMREAD_COLOR)
+    out = bb.dft_image(im, 0.1)
+    assert lsb(out, gold) <= 1 and np.abs(out.astype(int) - gold.astype(int)).mean() < 0.02
+    im = cv2.imread(os.path.join(GOLDEN, "spectrum_in_noise200.png"), cv2.IMREAD_COLOR)
+    gold = cv2.imread(os.path.join(GOLDEN, "spectrum_out_noise200_rows384_640.png"), cv2.IMREAD_COLOR)
+    assert lsb(bb.dft_image(im, 0.1)[384:640], gold) <= 1
+    # padded case (nsmooth = 5 -> reflect borders, crop) and float spectrum
+    img = synth("noise", 200, 300, 5)
+    ref_u8, ref_spec = oracle.dft_image(img, 5.0, want_f32=True)
+    out, spec = bb.dft_image(img, 5.0, want_f32=True)
+    assert spec.shape == ref_spec.shape
+    assert lsb(out, ref_u8) <= 1
+    big = ref_spec > 20.0            # |Re F| > 10: log is well conditioned there
+    assert np.abs(spec - ref_spec)[big].max() < 0.05
+
+
+def test_dft_image_4096_single_plane_shape(bb, oracle):
+    """BASELINE config 4 size (4096 x 4096, pad 0)."""
+    img = synth("noise", 4096, 4096, 0)
+    out = bb.dft_image(img, 0.1)
+    ref = oracle.dft_image(img, 0.1)
+    assert lsb(out, ref) <= 1

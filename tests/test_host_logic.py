@@ -1,0 +1,157 @@
+"""CPU: the C-ABI library loads and exports what include/blur_b200.h declares; host-side logic
+(sizing, taps, planner) matches the oracle; the device code run by the CPU emulator matches the
+oracle; the sharded host logic works over gloo with world_size 2.  No compute call needs a GPU."""
+import os
+import re
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+
+from util import Emulator, synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def emu():
+    return Emulator()
+
+
+def test_cabi_exports_every_declared_symbol():
+    import ctypes
+    hdr = open(os.path.join(ROOT, "include", "blur_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = sorted(set(re.findall(r"\b(blur_b200_[a-z0-9_]+)\s*\(", hdr)))
+    assert len(declared) >= 25
+    lib = ctypes.CDLL(os.path.join(ROOT, "blur_algorithms_b200", "libblur_b200.so"))
+    missing = [n for n in declared if not hasattr(lib, n)]
+    assert not missing, missing
+    from blur_algorithms_b200 import _lib
+    assert sorted(_lib.EXPORTED) == declared
+
+
+def test_sizing_helpers_match_oracle(oracle):
+    import blur_algorithms_b200 as bb
+    for n in range(0, 40000, 3):
+        assert bb.isValidSize(n) == oracle.is_valid_size(n)
+    for n in [1, 31, 32, 33, 100, 1000, 1110, 1950, 2324, 4004, 4126, 16714, 20000, 33098]:
+        assert bb.nearestTransformSize(n) == oracle.nearest_transform_size(n)
+    for s in [0.3, 0.5, 1, 2, 3, 5, 10, 25, 38.729833, 50, 100, 106.770783]:
+        assert bb.gaussian_window(s) == oracle.gaussian_window(s)
+        for m in (100, 330, 331, 332):
+            assert bb.gaussian_window(s, m) == oracle.gaussian_window(s, m)
+    for s, w, N in [(1, 5, 0), (2, 11, 32), (5, 31, 64), (50, 331, 17280), (25, 165, 2400), (7.5, 0, 0)]:
+        assert np.array_equal(bb.getGaussian(s, w, N), oracle.get_gaussian(s, w, N))
+    for rows, cols, s in [(1080, 1920, 5), (2160, 3840, 25), (16384, 16384, 50), (467, 700, 7.5)]:
+        g, o = bb.gauss_geometry(rows, cols, s), oracle.gauss_sizes(rows, cols, s)
+        assert (g["kSize"], g["pad"], g["n_col"], g["n_row"]) == (o["kSize"], o["pad"], o["n_col"], o["n_row"])
+    # SURVEY.md §8 table
+    assert bb.gauss_geometry(16384, 16384, 50) == dict(kSize=331, pad=165, n_col=17280, n_row=17280)
+    assert bb.gauss_geometry(2160, 3840, 25) == dict(kSize=165, pad=82, n_col=2400, n_row=4096)
+
+
+def test_compute_entry_points_fail_loudly_without_gpu():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    import blur_algorithms_b200 as bb
+    img = synth("noise", 64, 96)
+    with pytest.raises(bb.BlurB200Error):
+        bb.pffft_(img, 2.0)
+    with pytest.raises(bb.BlurB200Error):
+        bb.fastboxblur(img, 96, 64, 3, 9, 2)
+
+
+def test_argument_validation():
+    import blur_algorithms_b200 as bb
+    with pytest.raises(bb.BlurB200Error):
+        bb.pffft_(np.zeros((4, 4), np.uint8), 2.0)
+    with pytest.raises(bb.BlurB200Error):
+        bb.pocketfft_1D(np.zeros((4, 4, 3), np.float32), 2.0)
+    with pytest.raises(bb.BlurB200Error):
+        bb.Test(np.zeros((8, 8, 3), np.uint8), 1, 2.0)
+
+
+def test_every_valid_fft_length_plans_and_transforms(emu, oracle):
+    rng = np.random.default_rng(1)
+    sizes = [n for n in range(32, 28161, 32) if oracle.is_valid_size(n)]
+    assert len(sizes) == 82
+    for N in sizes:
+        a = rng.standard_normal(N).astype(np.float32)
+        b = rng.standard_normal(N).astype(np.float32)
+        code, outr, outi, spec = emu.fft_roundtrip(a, b)
+        assert code == 0, N
+        ref = np.fft.fft(a.astype(np.float64) + 1j * b.astype(np.float64))
+        assert np.abs(spec - ref).max() / np.abs(ref).max() < 3e-6, N
+        assert max(np.abs(outr - a).max(), np.abs(outi - b).max()) < 3e-5, N
+
+
+@pytest.mark.parametrize("rows,cols,sigma", [(64, 96, 2.0), (100, 75, 3.0), (135, 241, 6.0), (240, 320, 5.0), (467, 700, 7.5)])
+def test_device_code_on_cpu_matches_oracle(emu, oracle, rows, cols, sigma):
+    img = synth("noise", rows, cols, 5)
+    for mode in (0, 1):
+        ref, rp, _ = oracle.gauss_blur_1d(img, sigma, mode, want_f32=True)
+        for nparts in (1, 2, 3):
+            out, erp, _, _ = emu.gauss(img, sigma, mode, nparts)
+            assert np.abs(erp - rp).max() <= 255 * 1e-5          # float32 intermediate, 1e-5 relative
+            assert np.abs(out.astype(int) - ref.astype(int)).max() <= 1   # +-1 LSB
+
+
+def test_device_code_edge_inputs(emu, oracle):
+    for kind in ("const", "impulse", "stripes", "ramp"):
+        img = synth(kind, 96, 128)
+        ref = oracle.gauss_blur_1d(img, 2.5, 0)
+        out, _, _, _ = emu.gauss(img, 2.5, 0, 1)
+        assert np.abs(out.astype(int) - ref.astype(int)).max() <= 1, kind
+    out, _, _, _ = emu.gauss(synth("const", 40, 56), 3.0, 0, 1)
+    assert np.all(out == 200)
+
+
+_GLOO_WORKER = r'''
+import os, sys, ctypes as C
+import numpy as np, torch, torch.distributed as dist
+sys.path.insert(0, os.environ["BLUR_ROOT"]); sys.path.insert(0, os.path.join(os.environ["BLUR_ROOT"], "tests"))
+from util import Emulator, synth
+from oracle_lib import Oracle
+from blur_algorithms_b200.dist import ShardedGaussBlur
+dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%s" % os.environ["BLUR_PORT"],
+                        rank=int(os.environ["RANK"]), world_size=int(os.environ["WORLD_SIZE"]))
+rank, n = dist.get_rank(), dist.get_world_size()
+emu = Emulator()
+for rows, cols, sigma, mode in [(64, 96, 2.0, 0), (135, 241, 6.0, 1), (101, 75, 3.0, 0)]:
+    img = synth("noise", rows, cols, 9)
+    def row_pass(stripe, q):
+        assert emu.lib.emul_row_pass(stripe.data_ptr(), q.data_ptr(), rows, cols, sigma, mode, rank, n) == 0
+    def col_pass(q, out):
+        assert emu.lib.emul_col_pass(q.data_ptr(), out.data_ptr(), rows, cols, sigma, mode, rank, n) == 0
+    sb = ShardedGaussBlur(rows, cols, sigma, mode, device=torch.device("cpu"), row_pass=row_pass, col_pass=col_pass)
+    g = sb.geom
+    stripe = torch.from_numpy(np.ascontiguousarray(img[g.row0:g.row0 + g.valid_rows]))
+    mine = sb.run(stripe).contiguous()
+    # gather column stripes on every rank and compare with the single-process result
+    parts = [torch.zeros((rows, 2 * g.cpp, 3), dtype=torch.uint8) for _ in range(n)]
+    dist.all_gather(parts, sb.out_cols)
+    full = torch.cat(parts, 1)[:, :cols].numpy()
+    single, _, _, _ = emu.gauss(img, sigma, mode, 1)
+    assert np.array_equal(full, single), (rows, cols)
+    ref = Oracle().gauss_blur_1d(img, sigma, mode)
+    assert np.abs(full.astype(int) - ref.astype(int)).max() <= 1
+dist.barrier()
+print("rank", rank, "ok")
+'''
+
+
+def test_sharded_host_logic_gloo_world2(tmp_path):
+    import socket
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    script = tmp_path / "worker.py"
+    script.write_text(_GLOO_WORKER)
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE="2", BLUR_PORT=str(port), BLUR_ROOT=ROOT, OMP_NUM_THREADS="2")
+        procs.append(subprocess.Popen([sys.executable, str(script)], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT))
+    outs = [p.communicate(timeout=300)[0].decode() for p in procs]
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o
