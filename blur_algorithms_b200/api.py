@@ -120,10 +120,11 @@ class GaussPlan:
         else:
             check(lib.blur_b200_gauss_plan_create_sharded(C.byref(self._h), rows, cols, float(sigma), nyquist_mode,
                                                           device, rank, nranks))
-        info = (C.c_int64 * 16)()
+        info = (C.c_int64 * 24)()
         check(lib.blur_b200_gauss_plan_info(self._h, info))
         keys = ["kSize", "pad", "n_col", "n_row", "stripe_rows", "cpp", "row0", "valid_rows", "block_floats",
-                "launches_per_run", "threads_row", "threads_col", "batch_row", "batch_col", "smem_row", "smem_col"]
+                "launches_per_run", "threads_row", "threads_col", "batch_row", "batch_col", "smem_row", "smem_col",
+                "algo", "ols_L_row", "ols_L_col", "ols_V_row", "ols_V_col", "ols_nblocks_row", "ols_nblocks_col", "rqs"]
         self.info = {k: int(v) for k, v in zip(keys, info)}
 
     def close(self) -> None:

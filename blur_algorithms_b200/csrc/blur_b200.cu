@@ -16,6 +16,8 @@
 #include "../../include/blur_b200.h"
 #include "fft_launch.hpp"
 #include "fft_plan.hpp"
+#include "ols_launch.hpp"
+#include "ols_plan.hpp"
 
 using namespace blurb200;
 
@@ -89,6 +91,18 @@ __global__ void q_to_planar_kernel(const float* __restrict__ q, float* __restric
     const int cp = x >> 1, part = cp / cpp, cpl = cp - part * cpp;
     planar[(static_cast<size_t>(ch) * rows + r) * cols + x] =
         q[((static_cast<size_t>(part * 3 + ch) * cpp + cpl) * qrows + r) * 2 + (x & 1)];
+}
+
+// overlap-save Q [3][nparts][rqs][cpp][4][2] -> planar float [3][rows][cols]   (parity hook only)
+__global__ void q_ols_to_planar_kernel(const float* __restrict__ q, float* __restrict__ planar, int rows, int cols,
+                                       int cpp, int rqs, int nparts)
+{
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int r = blockIdx.y, ch = blockIdx.z;
+    if (x >= cols) return;
+    const int cp = x >> 1, part = cp / cpp, cpl = cp - part * cpp;
+    planar[(static_cast<size_t>(ch) * rows + r) * cols + x] =
+        q[(((static_cast<size_t>(ch) * nparts + part) * rqs + (r >> 2)) * cpp + cpl) * 8 + (r & 3) * 2 + (x & 1)];
 }
 
 // Reflect_101<uint8_t,C> (Utils.hpp:212-243): one thread per output byte.
@@ -297,6 +311,11 @@ struct blur_b200_plan {
     int stripe_rows = 0, cpp = 0, row0 = 0, valid_rows = 0, valid_ncp = 0;
     size_t block_floats = 0;          // floats per (stripe, part) block of Q
     AxisTables row, col;
+    int algo = 0;                     // 0 = full-length FFT per line, 1 = overlap-save blocks
+    OlsAxis ols_row{}, ols_col{};
+    float2 *d_ols_twa_row = nullptr, *d_ols_twa_col = nullptr, *d_ols_twb = nullptr;
+    float *d_ols_kt_row = nullptr, *d_ols_kt_col = nullptr;
+    int rqs = 0;                      // row quads per stripe (overlap-save Q)
     float* d_q = nullptr;             // [nranks] blocks
     uint8_t* d_u = nullptr;           // [3][2*cpp][rows]
     uint8_t* d_io = nullptr;          // staging for the host entry point (lazy)
@@ -348,6 +367,31 @@ int build_axis(AxisTables& ax, int N, double sigma, int ksize, int mode)
     return BLUR_B200_OK;
 }
 
+template <class T>
+int upload(T** dst, const std::vector<T>& v)
+{
+    CU_TRY(cudaMalloc(dst, sizeof(T) * v.size()));
+    CU_TRY(cudaMemcpy(*dst, v.data(), sizeof(T) * v.size(), cudaMemcpyHostToDevice));
+    return BLUR_B200_OK;
+}
+
+int build_ols_tables(blur_b200_plan* p, double sigma, int ksize)
+{
+    std::vector<float2> tw;
+    std::vector<float> kt;
+    make_ols_twiddles_b(tw);
+    int rc = upload(&p->d_ols_twb, tw);
+    if (rc) return rc;
+    make_ols_twiddles_a(p->ols_row.R0, tw);
+    if ((rc = upload(&p->d_ols_twa_row, tw))) return rc;
+    make_ols_kt(p->ols_row.R0, sigma, ksize, kt);
+    if ((rc = upload(&p->d_ols_kt_row, kt))) return rc;
+    make_ols_twiddles_a(p->ols_col.R0, tw);
+    if ((rc = upload(&p->d_ols_twa_col, tw))) return rc;
+    make_ols_kt(p->ols_col.R0, sigma, ksize, kt);
+    return upload(&p->d_ols_kt_col, kt);
+}
+
 int plan_create(blur_b200_plan** out, int rows, int cols, double sigma, int mode, int device, int rank, int nranks)
 {
     if (!out || rows < 1 || cols < 1 || !(sigma > 0) || (mode != 0 && mode != 1) || nranks < 1 || rank < 0 ||
@@ -365,20 +409,37 @@ int plan_create(blur_b200_plan** out, int rows, int cols, double sigma, int mode
     p->rank = rank; p->nranks = nranks;
     const int cp_total = (cols + 1) / 2;
     p->cpp = cdiv(cp_total, nranks);
+    // Algorithm: overlap-save blocks (ols_*) unless the Nyquist quirk of pffft is asked for (it is
+    // defined on the reference's full-length tile) or the kernel is too wide for the block menu.
+    const char* algo_env = std::getenv("BLUR_B200_ALGO");
+    int want_ols = mode == BLUR_B200_NYQUIST_EXACT ? 1 : 0;
+    if (algo_env && !std::strcmp(algo_env, "full")) want_ols = 0;
+    int force_r0 = 0;
+    if (const char* e = std::getenv("BLUR_B200_OLS_R0")) force_r0 = std::atoi(e);
+    if (want_ols && choose_ols_axis(cols, gg.pad, 1, p->ols_row, force_r0) &&
+        choose_ols_axis(rows, gg.pad, 4, p->ols_col, force_r0))
+        p->algo = 1;
     int sr = cdiv(rows, nranks);
-    sr += sr & 1;
+    sr = p->algo == 1 ? 4 * cdiv(sr, 4) : sr + (sr & 1);
     p->stripe_rows = sr;
+    p->rqs = sr / 4;
     p->row0 = rank * sr;
     p->valid_rows = std::max(0, std::min(sr, rows - p->row0));
     p->valid_ncp = std::max(0, std::min(p->cpp, cp_total - rank * p->cpp));
     p->block_floats = static_cast<size_t>(3) * p->cpp * sr * 2;
-    int rc = build_axis(p->row, gg.n_row, sigma, gg.ksize, mode);
-    if (rc == BLUR_B200_OK) rc = build_axis(p->col, gg.n_col, sigma, gg.ksize, mode);
+    int rc = BLUR_B200_OK;
+    if (p->algo == 1) {
+        rc = build_ols_tables(p, sigma, gg.ksize);
+    } else {
+        rc = build_axis(p->row, gg.n_row, sigma, gg.ksize, mode);
+        if (rc == BLUR_B200_OK) rc = build_axis(p->col, gg.n_col, sigma, gg.ksize, mode);
+    }
     if (rc != BLUR_B200_OK) { blur_b200_gauss_plan_destroy(p); return rc; }
     cudaDeviceProp prop;
     CU_TRY(cudaGetDeviceProperties(&prop, device));
     p->num_sms = prop.multiProcessorCount;
     CU_TRY(cudaMalloc(&p->d_q, sizeof(float) * p->block_floats * nranks));
+    CU_TRY(cudaMemset(p->d_q, 0, sizeof(float) * p->block_floats * nranks));   // phantom column of an odd width stays 0
     CU_TRY(cudaMalloc(&p->d_u, static_cast<size_t>(3) * 2 * p->cpp * rows));
     CU_TRY(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
     *out = p;
@@ -388,6 +449,18 @@ int plan_create(blur_b200_plan** out, int rows, int cols, double sigma, int mode
 int run_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, float* d_q, cudaStream_t st)
 {
     if (p->valid_rows <= 0) return BLUR_B200_OK;
+    if (p->algo == 1) {
+        OlsRowIO io{};
+        io.in = d_in_stripe; io.q = d_q;
+        io.rows = p->valid_rows; io.cols = p->cols;
+        io.npairs = cdiv(p->valid_rows, 2);
+        io.rqs = p->rqs; io.cpp = p->cpp; io.nparts = p->nranks;
+        io.ax = p->ols_row;
+        io.nunits = io.ax.nblocks * 3 * io.npairs;
+        CU_TRY(launch_ols_row(io, p->d_ols_twa_row, p->d_ols_twb, p->d_ols_kt_row, p->num_sms, st));
+        ++g_launches;
+        return BLUR_B200_OK;
+    }
     RowIO io{};
     io.in = d_in_stripe; io.q = d_q;
     io.rows = p->valid_rows; io.cols = p->cols; io.pad = p->gg.pad; io.N = p->row.g.N;
@@ -402,6 +475,17 @@ int run_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, float* d_q, cuda
 
 int run_col_pass_to_u(blur_b200_plan* p, const float* d_q_chunks, cudaStream_t st)
 {
+    if (p->algo == 1) {
+        OlsColIO io{};
+        io.u = p->d_u;
+        io.rows = p->rows; io.ncp = p->cpp; io.valid_ncp = p->valid_ncp; io.ucols = 2 * p->cpp;
+        io.ax = p->ols_col;
+        io.nunits = io.ax.nblocks * 3 * p->cpp;
+        CU_TRY(launch_ols_col(io, d_q_chunks, p->nranks * p->rqs, p->d_ols_twa_col, p->d_ols_twb, p->d_ols_kt_col,
+                              p->num_sms, st));
+        ++g_launches;
+        return BLUR_B200_OK;
+    }
     ColIO io{};
     io.q = reinterpret_cast<const float2*>(d_q_chunks);
     io.chunk_stride = p->block_floats / 2;
@@ -486,12 +570,14 @@ void blur_b200_gauss_plan_destroy(blur_b200_plan* p)
     cudaSetDevice(p->device);
     cudaFree(p->row.d_tw); cudaFree(p->row.d_kt);
     cudaFree(p->col.d_tw); cudaFree(p->col.d_kt);
+    cudaFree(p->d_ols_twa_row); cudaFree(p->d_ols_twa_col); cudaFree(p->d_ols_twb);
+    cudaFree(p->d_ols_kt_row); cudaFree(p->d_ols_kt_col);
     cudaFree(p->d_q); cudaFree(p->d_u); cudaFree(p->d_io);
     if (p->stream) cudaStreamDestroy(p->stream);
     delete p;
 }
 
-int blur_b200_gauss_plan_info(const blur_b200_plan* p, int64_t info[16])
+int blur_b200_gauss_plan_info(const blur_b200_plan* p, int64_t info[24])
 {
     if (!p || !info) return BLUR_B200_EINVAL;
     info[0] = p->gg.ksize; info[1] = p->gg.pad; info[2] = p->gg.n_col; info[3] = p->gg.n_row;
@@ -501,6 +587,15 @@ int blur_b200_gauss_plan_info(const blur_b200_plan* p, int64_t info[16])
     info[10] = p->row.shape.threads; info[11] = p->col.shape.threads;
     info[12] = p->row.shape.batch; info[13] = p->col.shape.batch;
     info[14] = static_cast<int64_t>(p->row.shape.smem_bytes); info[15] = static_cast<int64_t>(p->col.shape.smem_bytes);
+    info[16] = p->algo;
+    info[17] = p->ols_row.L; info[18] = p->ols_col.L;
+    info[19] = p->ols_row.V; info[20] = p->ols_col.V;
+    info[21] = p->ols_row.nblocks; info[22] = p->ols_col.nblocks;
+    info[23] = p->rqs;
+    if (p->algo == 1) {
+        info[10] = info[11] = 64; info[12] = info[13] = 1;
+        info[14] = 8 * p->ols_row.L + 16; info[15] = 8 * p->ols_col.L + 16;
+    }
     return BLUR_B200_OK;
 }
 
@@ -563,7 +658,10 @@ int blur_b200_gauss_rowpass_f32(blur_b200_plan* p, const uint8_t* d_in, float* d
     int rc = run_row_pass(p, d_in, p->d_q, st);
     if (rc) return rc;
     dim3 grid(cdiv(p->cols, 256), p->rows, 3);
-    q_to_planar_kernel<<<grid, 256, 0, st>>>(p->d_q, d_planar, p->rows, p->cols, p->cpp, p->stripe_rows);
+    if (p->algo == 1)
+        q_ols_to_planar_kernel<<<grid, 256, 0, st>>>(p->d_q, d_planar, p->rows, p->cols, p->cpp, p->rqs, p->nranks);
+    else
+        q_to_planar_kernel<<<grid, 256, 0, st>>>(p->d_q, d_planar, p->rows, p->cols, p->cpp, p->stripe_rows);
     CU_TRY(cudaGetLastError());
     ++g_launches;
     return BLUR_B200_OK;

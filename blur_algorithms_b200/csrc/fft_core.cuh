@@ -26,8 +26,11 @@
 #define BLUR_DEV_INLINE __host__ __device__ __forceinline__
 #else
 #define BLUR_DEV_INLINE inline
+#ifndef BLUR_FLOAT2_DEFINED
+#define BLUR_FLOAT2_DEFINED
 struct float2 { float x, y; };
 static inline float2 make_float2(float a, float b) { float2 r; r.x = a; r.y = b; return r; }
+#endif
 #endif
 
 namespace blurb200 {

@@ -1,0 +1,15 @@
+// ols_launch.hpp — host-callable launchers of the overlap-save kernels (one TU per IO type so
+// the instantiations compile in parallel).
+#pragma once
+#include <cuda_runtime.h>
+#include "ols_core.cuh"
+
+namespace blurb200 {
+// grid = min(nunits, num_sms * resident CTAs); returns the CUDA error of the launch.
+cudaError_t launch_ols_row(const OlsRowIO& io, const float2* twA, const float2* twB, const float* kt, int num_sms,
+                           cudaStream_t stream);
+// d_q: Q as received [3][nranks][rqs][cpp][8] floats; rq_total = nranks * rqs
+cudaError_t launch_ols_col(const OlsColIO& io, const float* d_q, int rq_total, const float2* twA, const float2* twB,
+                           const float* kt, int num_sms, cudaStream_t stream);
+int ols_resident_ctas(int R0);
+}  // namespace blurb200

@@ -1,0 +1,81 @@
+// ols_plan.hpp — host-side planning of the overlap-save passes: block length choice and the
+// twiddle / kernel-spectrum tables.  Pure C++ (the CPU emulator uses it too).
+#pragma once
+#include <cmath>
+#include <vector>
+
+#include "fft_plan.hpp"
+#include "ols_core.cuh"
+
+namespace blurb200 {
+
+static const int kOlsRadices[] = {4, 6, 8, 12, 16, 24, 32};
+
+// Picks the block length with the least total FFT work for lines of `len` samples and a
+// reflect pad of `pad`.  `align` = granularity of a block's first sample (4 for the column pass:
+// TMA boxes start on a row quad).  Returns false if no block length leaves at least a quarter
+// of each block as valid output (very wide kernels: the caller uses the full-length path).
+inline bool choose_ols_axis(int len, int pad, int align, OlsAxis& ax, int force_r0 = 0)
+{
+    ax = OlsAxis{};
+    double best = 1e300;
+    for (int r0 : kOlsRadices) {
+        if (force_r0 && r0 != force_r0) continue;
+        const int L = 256 * r0;
+        const int halo = ((pad + align - 1) / align) * align;
+        const int V = L - 2 * halo;
+        if (V < L / 4 && !force_r0) continue;
+        if (V <= 0) continue;
+        const int nb = (len + V - 1) / V;
+        // work ~ samples transformed x (log2 L + constant for the passes' fixed costs)
+        const double cost = static_cast<double>(nb) * L * (std::log2(static_cast<double>(L)) + 6.0);
+        if (cost < best) {
+            best = cost;
+            ax.R0 = r0; ax.L = L; ax.halo = halo; ax.V = V; ax.nblocks = nb; ax.len = len; ax.pad = pad;
+        }
+    }
+    return ax.R0 != 0;
+}
+
+// twA[(q-1)*256 + t] = exp(-2 pi i q t / L), q = 1..R0-1, t < 256
+inline void make_ols_twiddles_a(int R0, std::vector<float2>& tw)
+{
+    const int L = 256 * R0;
+    tw.resize(static_cast<size_t>(std::max(1, R0 - 1)) * 256);
+    for (int q = 1; q < R0; ++q)
+        for (int t = 0; t < 256; ++t) {
+            const double a = -2.0 * 3.14159265358979323846 * static_cast<double>(q) * t / L;
+            tw[static_cast<size_t>(q - 1) * 256 + t] = make_float2(static_cast<float>(std::cos(a)), static_cast<float>(std::sin(a)));
+        }
+}
+
+// twB[(q-1)*16 + t] = exp(-2 pi i q t / 256), q = 1..15, t < 16
+inline void make_ols_twiddles_b(std::vector<float2>& tw)
+{
+    tw.resize(15 * 16);
+    for (int q = 1; q < 16; ++q)
+        for (int t = 0; t < 16; ++t) {
+            const double a = -2.0 * 3.14159265358979323846 * static_cast<double>(q) * t / 256.0;
+            tw[static_cast<size_t>(q - 1) * 16 + t] = make_float2(static_cast<float>(std::cos(a)), static_cast<float>(std::sin(a)));
+        }
+}
+
+// kt[q * (16 R0) + u] = Re K_L[k0 + R0*(k1 + 16 q)] * (1/L),  u = 16*k0 + k1.
+// K_L = DFT of the reference's rotated float taps (Source.cpp:75-102) zero-extended to L; only
+// its real part is used, like Source.cpp:362,423.  1/L folded in as a float product (:506-507).
+inline void make_ols_kt(int R0, double sigma, int ksize, std::vector<float>& kt)
+{
+    const int L = 256 * R0, W = 16 * R0;
+    std::vector<double> K;
+    kernel_spectrum(sigma, ksize, L, K);
+    const float scaler = 1.f / static_cast<float>(L);
+    kt.resize(static_cast<size_t>(L));
+    for (int u = 0; u < W; ++u)
+        for (int q = 0; q < 16; ++q) {
+            const int k0 = u >> 4, k1 = u & 15;
+            const int k = k0 + R0 * (k1 + 16 * q);
+            kt[static_cast<size_t>(q) * W + u] = static_cast<float>(K[k]) * scaler;
+        }
+}
+
+}  // namespace blurb200

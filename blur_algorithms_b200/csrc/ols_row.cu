@@ -1,0 +1,53 @@
+// ols_row.cu — row-pass instantiations of the overlap-save kernel.
+#include "ols_kernels.cuh"
+#include "ols_launch.hpp"
+
+namespace blurb200 {
+
+template <int R0>
+static cudaError_t launch_row(const OlsRowIO& io, const float2* twA, const float2* twB, const float* kt, int num_sms,
+                              cudaStream_t stream)
+{
+    static bool configured = false;
+    constexpr int smem = ols_smem_bytes<R0>();
+    if (!configured) {
+        cudaError_t e = cudaFuncSetAttribute(ols_row_kernel<R0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) return e;
+        configured = true;
+    }
+    const int grid = std::min(io.nunits, num_sms * ols_ctas_per_sm<R0>());
+    if (grid <= 0) return cudaSuccess;
+    ols_row_kernel<R0><<<grid, kOlsThreads, smem, stream>>>(io, twA, twB, kt);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_ols_row(const OlsRowIO& io, const float2* twA, const float2* twB, const float* kt, int num_sms,
+                           cudaStream_t stream)
+{
+    switch (io.ax.R0) {
+    case 4: return launch_row<4>(io, twA, twB, kt, num_sms, stream);
+    case 6: return launch_row<6>(io, twA, twB, kt, num_sms, stream);
+    case 8: return launch_row<8>(io, twA, twB, kt, num_sms, stream);
+    case 12: return launch_row<12>(io, twA, twB, kt, num_sms, stream);
+    case 16: return launch_row<16>(io, twA, twB, kt, num_sms, stream);
+    case 24: return launch_row<24>(io, twA, twB, kt, num_sms, stream);
+    case 32: return launch_row<32>(io, twA, twB, kt, num_sms, stream);
+    default: return cudaErrorInvalidValue;
+    }
+}
+
+int ols_resident_ctas(int R0)
+{
+    switch (R0) {
+    case 4: return ols_ctas_per_sm<4>();
+    case 6: return ols_ctas_per_sm<6>();
+    case 8: return ols_ctas_per_sm<8>();
+    case 12: return ols_ctas_per_sm<12>();
+    case 16: return ols_ctas_per_sm<16>();
+    case 24: return ols_ctas_per_sm<24>();
+    case 32: return ols_ctas_per_sm<32>();
+    default: return 0;
+    }
+}
+
+}  // namespace blurb200

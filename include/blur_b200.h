@@ -75,8 +75,12 @@ void blur_b200_gauss_plan_destroy(blur_b200_plan *plan);
 /* info[0]=kSize [1]=pad [2]=n_col [3]=n_row [4]=stripe_rows [5]=cpp (column pairs per rank)
  * [6]=rank's first row [7]=rank's valid rows [8]=floats per (stripe,part) block of Q
  * [9]=kernel launches per run [10]=threads row kernel [11]=threads col kernel
- * [12]=batch row [13]=batch col [14]=smem row [15]=smem col */
-int blur_b200_gauss_plan_info(const blur_b200_plan *plan, int64_t info[16]);
+ * [12]=batch row [13]=batch col [14]=smem row [15]=smem col
+ * [16]=algorithm: 0 = one full-length FFT per line (the reference's tile, fft_kernels.cuh),
+ *                 1 = overlap-save blocks (ols_kernels.cuh)
+ * [17],[18]=overlap-save block length row/col pass [19],[20]=valid outputs per block
+ * [21],[22]=blocks per line [23]=row quads per stripe */
+int blur_b200_gauss_plan_info(const blur_b200_plan *plan, int64_t info[24]);
 
 /* Whole blur, device resident: d_in and d_out are uint8 [rows][cols][3]; may alias (in place,
  * like image.data in the reference). */
