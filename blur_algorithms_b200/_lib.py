@@ -38,6 +38,7 @@ def _load() -> C.CDLL:
         "blur_b200_gaussian_window": (i32, [f64, i32]),
         "blur_b200_get_gaussian": (i32, [vp, f64, i32, i32]),
         "blur_b200_gauss_geometry": (i32, [i32, i32, f64, pi32]),
+        "blur_b200_gauss_shard_geometry": (i32, [i32, i32, f64, i32, i32, i32, C.POINTER(C.c_int64)]),
         "blur_b200_gauss_plan_create": (i32, [C.POINTER(vp), i32, i32, f64, i32, i32]),
         "blur_b200_gauss_plan_create_sharded": (i32, [C.POINTER(vp), i32, i32, f64, i32, i32, i32, i32]),
         "blur_b200_gauss_plan_destroy": (None, [vp]),
@@ -71,7 +72,7 @@ lib = _load()
 EXPORTED = [
     "blur_b200_strerror", "blur_b200_last_cuda_error", "blur_b200_is_valid_size",
     "blur_b200_nearest_transform_size", "blur_b200_gaussian_window", "blur_b200_get_gaussian",
-    "blur_b200_gauss_geometry", "blur_b200_gauss_plan_create", "blur_b200_gauss_plan_create_sharded",
+    "blur_b200_gauss_geometry", "blur_b200_gauss_shard_geometry", "blur_b200_gauss_plan_create", "blur_b200_gauss_plan_create_sharded",
     "blur_b200_gauss_plan_destroy", "blur_b200_gauss_plan_info", "blur_b200_gauss_run_device",
     "blur_b200_gauss_run_host", "blur_b200_gauss_u8c3", "blur_b200_gauss_row_pass",
     "blur_b200_gauss_col_pass", "blur_b200_gauss_rowpass_f32", "blur_b200_fastboxblur_device",

@@ -93,16 +93,61 @@ __global__ void q_to_planar_kernel(const float* __restrict__ q, float* __restric
         q[((static_cast<size_t>(part * 3 + ch) * cpp + cpl) * qrows + r) * 2 + (x & 1)];
 }
 
-// overlap-save Q [3][nparts][rqs][cpp][4][2] -> planar float [3][rows][cols]   (parity hook only)
+// overlap-save U [3][noct][rows][8] (uint8) -> out [rows][out_cols][3].  Tile = 64 rows x 4 octets
+// (32 columns): 12 runs of 512 contiguous bytes in, 64 runs of 96 contiguous bytes out.
+// Replaces the reference's second flip_block (Source.cpp:562) and interleave_BGR (:567).
+constexpr int kOctTileR = 64;
+__global__ void __launch_bounds__(256)
+interleave_oct_kernel(const uint8_t* __restrict__ u, uint8_t* __restrict__ out, int rows, int noct,
+                      int ncols /* valid columns to emit */, int out_cols /* row pitch of out, in pixels */, int vec)
+{
+    __shared__ __align__(8) uint8_t tile[3][4][kOctTileR][8];       // 6 KB
+    const int o0 = blockIdx.x * 4, r0 = blockIdx.y * kOctTileR;
+    const int tid = threadIdx.x;
+    for (int i = tid; i < 12 * kOctTileR; i += 256) {
+        const int line = i / kOctTileR, r = i - line * kOctTileR;
+        const int ch = line >> 2, o = line & 3;
+        if (o0 + o < noct && r0 + r < rows)
+            *reinterpret_cast<uint2*>(&tile[ch][o][r][0]) =
+                *reinterpret_cast<const uint2*>(u + ((static_cast<size_t>(ch) * noct + o0 + o) * rows + r0 + r) * 8);
+    }
+    __syncthreads();
+    const int c0 = o0 * 8;
+    const int nc = min(32, ncols - c0);
+    if (nc <= 0) return;
+    if (vec && nc == 32) {
+        for (int i = tid; i < kOctTileR * 24; i += 256) {
+            const int r = i / 24, w = i - r * 24;
+            if (r0 + r >= rows) continue;
+            uint32_t v = 0;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int b = 4 * w + k, c = b / 3, ch = b - c * 3;
+                v |= static_cast<uint32_t>(tile[ch][c >> 3][r][c & 7]) << (8 * k);
+            }
+            *reinterpret_cast<uint32_t*>(out + (static_cast<size_t>(r0 + r) * out_cols + c0) * 3 + 4 * w) = v;
+        }
+    } else {
+        const int nbytes = nc * 3;
+        for (int i = tid; i < kOctTileR * 96; i += 256) {
+            const int r = i / 96, b = i - r * 96;
+            if (b >= nbytes || r0 + r >= rows) continue;
+            const int c = b / 3, ch = b - c * 3;
+            out[(static_cast<size_t>(r0 + r) * out_cols + c0) * 3 + b] = tile[ch][c >> 3][r][c & 7];
+        }
+    }
+}
+
+// overlap-save Q [3][nparts][srows][qpitch] -> planar float [3][rows][cols]   (parity hook only)
 __global__ void q_ols_to_planar_kernel(const float* __restrict__ q, float* __restrict__ planar, int rows, int cols,
-                                       int cpp, int rqs, int nparts)
+                                       int qpitch, int cpart, int srows, int nparts)
 {
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
     const int r = blockIdx.y, ch = blockIdx.z;
     if (x >= cols) return;
-    const int cp = x >> 1, part = cp / cpp, cpl = cp - part * cpp;
+    const int part = nparts == 1 ? 0 : x / cpart, xl = x - part * cpart;
     planar[(static_cast<size_t>(ch) * rows + r) * cols + x] =
-        q[(((static_cast<size_t>(ch) * nparts + part) * rqs + (r >> 2)) * cpp + cpl) * 8 + (r & 3) * 2 + (x & 1)];
+        q[((static_cast<size_t>(ch) * nparts + part) * srows + r) * qpitch + xl];
 }
 
 // Reflect_101<uint8_t,C> (Utils.hpp:212-243): one thread per output byte.
@@ -315,7 +360,7 @@ struct blur_b200_plan {
     OlsAxis ols_row{}, ols_col{};
     float2 *d_ols_twa_row = nullptr, *d_ols_twa_col = nullptr, *d_ols_twb = nullptr;
     float *d_ols_kt_row = nullptr, *d_ols_kt_col = nullptr;
-    int rqs = 0;                      // row quads per stripe (overlap-save Q)
+    int qpitch = 0, cpart = 0;        // overlap-save Q: floats per row / image columns per part
     float* d_q = nullptr;             // [nranks] blocks
     uint8_t* d_u = nullptr;           // [3][2*cpp][rows]
     uint8_t* d_io = nullptr;          // staging for the host entry point (lazy)
@@ -407,26 +452,11 @@ int plan_create(blur_b200_plan** out, int rows, int cols, double sigma, int mode
     if (!p) return BLUR_B200_ENOMEM;
     p->device = device; p->rows = rows; p->cols = cols; p->sigma = sigma; p->mode = mode; p->gg = gg;
     p->rank = rank; p->nranks = nranks;
-    const int cp_total = (cols + 1) / 2;
-    p->cpp = cdiv(cp_total, nranks);
-    // Algorithm: overlap-save blocks (ols_*) unless the Nyquist quirk of pffft is asked for (it is
-    // defined on the reference's full-length tile) or the kernel is too wide for the block menu.
-    const char* algo_env = std::getenv("BLUR_B200_ALGO");
-    int want_ols = mode == BLUR_B200_NYQUIST_EXACT ? 1 : 0;
-    if (algo_env && !std::strcmp(algo_env, "full")) want_ols = 0;
-    int force_r0 = 0;
-    if (const char* e = std::getenv("BLUR_B200_OLS_R0")) force_r0 = std::atoi(e);
-    if (want_ols && choose_ols_axis(cols, gg.pad, 1, p->ols_row, force_r0) &&
-        choose_ols_axis(rows, gg.pad, 4, p->ols_col, force_r0))
-        p->algo = 1;
-    int sr = cdiv(rows, nranks);
-    sr = p->algo == 1 ? 4 * cdiv(sr, 4) : sr + (sr & 1);
-    p->stripe_rows = sr;
-    p->rqs = sr / 4;
-    p->row0 = rank * sr;
-    p->valid_rows = std::max(0, std::min(sr, rows - p->row0));
-    p->valid_ncp = std::max(0, std::min(p->cpp, cp_total - rank * p->cpp));
-    p->block_floats = static_cast<size_t>(3) * p->cpp * sr * 2;
+    const ShardGeom sg = shard_geometry(gg, mode, rank, nranks);
+    p->algo = sg.algo; p->ols_row = sg.ols_row; p->ols_col = sg.ols_col;
+    p->cpp = sg.cpp; p->qpitch = sg.qpitch; p->cpart = sg.cpart;
+    p->stripe_rows = sg.stripe_rows; p->row0 = sg.row0; p->valid_rows = sg.valid_rows; p->valid_ncp = sg.valid_ncp;
+    p->block_floats = sg.block_floats;
     int rc = BLUR_B200_OK;
     if (p->algo == 1) {
         rc = build_ols_tables(p, sigma, gg.ksize);
@@ -454,7 +484,7 @@ int run_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, float* d_q, cuda
         io.in = d_in_stripe; io.q = d_q;
         io.rows = p->valid_rows; io.cols = p->cols;
         io.npairs = cdiv(p->valid_rows, 2);
-        io.rqs = p->rqs; io.cpp = p->cpp; io.nparts = p->nranks;
+        io.srows = p->stripe_rows; io.qpitch = p->qpitch; io.cpart = p->cpart; io.nparts = p->nranks;
         io.ax = p->ols_row;
         io.nunits = io.ax.nblocks * 3 * io.npairs;
         CU_TRY(launch_ols_row(io, p->d_ols_twa_row, p->d_ols_twb, p->d_ols_kt_row, p->num_sms, st));
@@ -478,11 +508,12 @@ int run_col_pass_to_u(blur_b200_plan* p, const float* d_q_chunks, cudaStream_t s
     if (p->algo == 1) {
         OlsColIO io{};
         io.u = p->d_u;
-        io.rows = p->rows; io.ncp = p->cpp; io.valid_ncp = p->valid_ncp; io.ucols = 2 * p->cpp;
+        io.rows = p->rows;
+        io.noct = std::min(p->qpitch / 8, cdiv(std::max(0, p->cols - p->rank * p->cpart), 8));
         io.ax = p->ols_col;
-        io.nunits = io.ax.nblocks * 3 * p->cpp;
-        CU_TRY(launch_ols_col(io, d_q_chunks, p->nranks * p->rqs, p->d_ols_twa_col, p->d_ols_twb, p->d_ols_kt_col,
-                              p->num_sms, st));
+        io.nunits = io.ax.nblocks * 3 * io.noct;
+        CU_TRY(launch_ols_col(io, d_q_chunks, p->qpitch, p->nranks * p->stripe_rows, p->d_ols_twa_col, p->d_ols_twb,
+                              p->d_ols_kt_col, p->num_sms, st));
         ++g_launches;
         return BLUR_B200_OK;
     }
@@ -504,6 +535,15 @@ int run_col_pass_to_u(blur_b200_plan* p, const float* d_q_chunks, cudaStream_t s
 int run_interleave(blur_b200_plan* p, uint8_t* d_out, int ncols, int out_cols, cudaStream_t st)
 {
     if (ncols <= 0) return BLUR_B200_OK;
+    if (p->algo == 1) {
+        const int noct = std::min(p->qpitch / 8, cdiv(std::max(0, p->cols - p->rank * p->cpart), 8));
+        const int vec = (static_cast<size_t>(out_cols) * 3 % 4 == 0) && (reinterpret_cast<uintptr_t>(d_out) % 4 == 0);
+        dim3 g(cdiv(noct, 4), cdiv(p->rows, kOctTileR));
+        interleave_oct_kernel<<<g, 256, 0, st>>>(p->d_u, d_out, p->rows, noct, std::min(ncols, noct * 8), out_cols, vec);
+        CU_TRY(cudaGetLastError());
+        ++g_launches;
+        return BLUR_B200_OK;
+    }
     dim3 grid(cdiv(ncols, kIlTileC), cdiv(p->rows, kIlTileR));
     interleave_u8_kernel<<<grid, 256, 0, st>>>(p->d_u, d_out, p->rows, 2 * p->cpp, ncols, out_cols);
     CU_TRY(cudaGetLastError());
@@ -553,6 +593,17 @@ int blur_b200_gauss_geometry(int rows, int cols, double sigma, int out[4])
     return BLUR_B200_OK;
 }
 
+int blur_b200_gauss_shard_geometry(int rows, int cols, double sigma, int nyquist_mode, int rank, int nranks,
+                                   int64_t out[8])
+{
+    if (!out || rows < 1 || cols < 1 || !(sigma > 0) || nranks < 1 || rank < 0 || rank >= nranks) return BLUR_B200_EINVAL;
+    const ShardGeom g = shard_geometry(gauss_geometry(rows, cols, sigma), nyquist_mode, rank, nranks);
+    out[0] = g.algo; out[1] = g.stripe_rows; out[2] = g.cpp; out[3] = g.row0; out[4] = g.valid_rows;
+    out[5] = std::max(0, std::min(2 * g.cpp, cols - rank * 2 * g.cpp));
+    out[6] = static_cast<int64_t>(g.block_floats); out[7] = g.qpitch;
+    return BLUR_B200_OK;
+}
+
 int blur_b200_gauss_plan_create(blur_b200_plan** plan, int rows, int cols, double sigma, int nyquist_mode, int device)
 {
     return plan_create(plan, rows, cols, sigma, nyquist_mode, device, 0, 1);
@@ -591,7 +642,7 @@ int blur_b200_gauss_plan_info(const blur_b200_plan* p, int64_t info[24])
     info[17] = p->ols_row.L; info[18] = p->ols_col.L;
     info[19] = p->ols_row.V; info[20] = p->ols_col.V;
     info[21] = p->ols_row.nblocks; info[22] = p->ols_col.nblocks;
-    info[23] = p->rqs;
+    info[23] = p->qpitch;
     if (p->algo == 1) {
         info[10] = info[11] = 64; info[12] = info[13] = 1;
         info[14] = 8 * p->ols_row.L + 16; info[15] = 8 * p->ols_col.L + 16;
@@ -659,7 +710,8 @@ int blur_b200_gauss_rowpass_f32(blur_b200_plan* p, const uint8_t* d_in, float* d
     if (rc) return rc;
     dim3 grid(cdiv(p->cols, 256), p->rows, 3);
     if (p->algo == 1)
-        q_ols_to_planar_kernel<<<grid, 256, 0, st>>>(p->d_q, d_planar, p->rows, p->cols, p->cpp, p->rqs, p->nranks);
+        q_ols_to_planar_kernel<<<grid, 256, 0, st>>>(p->d_q, d_planar, p->rows, p->cols, p->qpitch, p->cpart,
+                                                     p->stripe_rows, p->nranks);
     else
         q_to_planar_kernel<<<grid, 256, 0, st>>>(p->d_q, d_planar, p->rows, p->cols, p->cpp, p->stripe_rows);
     CU_TRY(cudaGetLastError());

@@ -22,14 +22,14 @@ EncodeFn get_encode()
     return fn;
 }
 
-// Q [3][rq_total][cpp][8] floats as a 3-D tensor (8*cpp, rq_total, 3); box = (8, kOlsBoxRows, 1):
-// 128 sectors of 32 bytes = rows 4*rq .. 4*rq+511 of one column pair, contiguous in shared memory.
-cudaError_t encode_q(CUtensorMap* map, const float* d_q, int cpp, int rq_total)
+// Q [3][rows_total][qpitch] floats as a 3-D tensor; box = (8 columns, kOlsBoxRows rows, 1): one
+// 32-byte sector per image row, landing contiguously in shared memory.
+cudaError_t encode_q(CUtensorMap* map, const float* d_q, int qpitch, int rows_total)
 {
     EncodeFn enc = get_encode();
     if (!enc) return cudaErrorNotSupported;
-    const cuuint64_t dims[3] = {static_cast<cuuint64_t>(cpp) * 8, static_cast<cuuint64_t>(rq_total), 3};
-    const cuuint64_t strides[2] = {static_cast<cuuint64_t>(cpp) * 32, static_cast<cuuint64_t>(cpp) * 32 * rq_total};
+    const cuuint64_t dims[3] = {static_cast<cuuint64_t>(qpitch), static_cast<cuuint64_t>(rows_total), 3};
+    const cuuint64_t strides[2] = {static_cast<cuuint64_t>(qpitch) * 4, static_cast<cuuint64_t>(qpitch) * 4 * rows_total};
     const cuuint32_t box[3] = {8, kOlsBoxRows, 1};
     const cuuint32_t estr[3] = {1, 1, 1};
     const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, const_cast<float*>(d_q), dims, strides, box, estr,
@@ -44,23 +44,23 @@ static cudaError_t launch_col(const OlsColIO& io, const CUtensorMap& map, const 
                               const float* kt, int num_sms, cudaStream_t stream)
 {
     static bool configured = false;
-    constexpr int smem = ols_smem_bytes<R0>();
+    constexpr int smem = ols_smem_bytes<R0, 4>();
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(ols_col_kernel<R0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    const int grid = std::min(io.nunits, num_sms * ols_ctas_per_sm<R0>());
+    const int grid = std::min(io.nunits, num_sms * ols_ctas_per_sm<R0, 4>());
     if (grid <= 0) return cudaSuccess;
-    ols_col_kernel<R0><<<grid, kOlsThreads, smem, stream>>>(io, map, twA, twB, kt);
+    ols_col_kernel<R0><<<grid, 4 * kOlsThreads, smem, stream>>>(io, map, twA, twB, kt);
     return cudaGetLastError();
 }
 
-cudaError_t launch_ols_col(const OlsColIO& io, const float* d_q, int rq_total, const float2* twA, const float2* twB,
-                           const float* kt, int num_sms, cudaStream_t stream)
+cudaError_t launch_ols_col(const OlsColIO& io, const float* d_q, int qpitch, int rows_total, const float2* twA,
+                           const float2* twB, const float* kt, int num_sms, cudaStream_t stream)
 {
     CUtensorMap map;
-    cudaError_t e = encode_q(&map, d_q, io.ncp, rq_total);
+    cudaError_t e = encode_q(&map, d_q, qpitch, rows_total);
     if (e != cudaSuccess) return e;
     switch (io.ax.R0) {
     case 4: return launch_col<4>(io, map, twA, twB, kt, num_sms, stream);

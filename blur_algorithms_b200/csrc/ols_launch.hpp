@@ -8,8 +8,8 @@ namespace blurb200 {
 // grid = min(nunits, num_sms * resident CTAs); returns the CUDA error of the launch.
 cudaError_t launch_ols_row(const OlsRowIO& io, const float2* twA, const float2* twB, const float* kt, int num_sms,
                            cudaStream_t stream);
-// d_q: Q as received [3][nranks][rqs][cpp][8] floats; rq_total = nranks * rqs
-cudaError_t launch_ols_col(const OlsColIO& io, const float* d_q, int rq_total, const float2* twA, const float2* twB,
-                           const float* kt, int num_sms, cudaStream_t stream);
+// d_q: Q as received [3][rows_total][qpitch] floats; rows_total = nranks * srows
+cudaError_t launch_ols_col(const OlsColIO& io, const float* d_q, int qpitch, int rows_total, const float2* twA,
+                           const float2* twB, const float* kt, int num_sms, cudaStream_t stream);
 int ols_resident_ctas(int R0);
 }  // namespace blurb200

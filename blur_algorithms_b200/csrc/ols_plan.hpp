@@ -2,6 +2,8 @@
 // twiddle / kernel-spectrum tables.  Pure C++ (the CPU emulator uses it too).
 #pragma once
 #include <cmath>
+#include <cstdlib>
+#include <cstring>
 #include <vector>
 
 #include "fft_plan.hpp"
@@ -12,15 +14,15 @@ namespace blurb200 {
 static const int kOlsRadices[] = {4, 6, 8, 12, 16, 24, 32};
 
 // Picks the block length with the least total FFT work for lines of `len` samples and a
-// reflect pad of `pad`.  `align` = granularity of a block's first sample (4 for the column pass:
-// TMA boxes start on a row quad).  Returns false if no block length leaves at least a quarter
+// reflect pad of `pad`.  `align` = granularity of a block's first sample; max_r0 caps the block
+// length (the column pass keeps four blocks in shared memory at once).  Returns false if no block length leaves at least a quarter
 // of each block as valid output (very wide kernels: the caller uses the full-length path).
-inline bool choose_ols_axis(int len, int pad, int align, OlsAxis& ax, int force_r0 = 0)
+inline bool choose_ols_axis(int len, int pad, int align, int max_r0, OlsAxis& ax, int force_r0 = 0)
 {
     ax = OlsAxis{};
     double best = 1e300;
     for (int r0 : kOlsRadices) {
-        if (force_r0 && r0 != force_r0) continue;
+        if ((force_r0 && r0 != force_r0) || r0 > max_r0) continue;
         const int L = 256 * r0;
         const int halo = ((pad + align - 1) / align) * align;
         const int V = L - 2 * halo;
@@ -35,6 +37,50 @@ inline bool choose_ols_axis(int len, int pad, int align, OlsAxis& ax, int force_
         }
     }
     return ax.R0 != 0;
+}
+
+// How one image is cut over `nranks` GPUs (nranks = 1: the whole image) and which algorithm
+// runs: the single source of truth for blur_b200.cu, the CPU emulator and dist.py.
+struct ShardGeom {
+    int algo;            // 0 = one full-length FFT per line (fft_kernels.cuh), 1 = overlap-save
+    OlsAxis ols_row, ols_col;
+    int stripe_rows;     // image rows per rank in the row pass (capacity; the last rank may own fewer)
+    int cpp;             // column pairs per rank in the column pass
+    int qpitch, cpart;   // overlap-save Q: floats per Q row / image columns per part (= 2*cpp)
+    int row0, valid_rows, valid_ncp;
+    size_t block_floats; // floats per (stripe, part) block of Q = 3 * stripe_rows * 2*cpp
+};
+
+inline ShardGeom shard_geometry(const GaussGeometry& gg, int nyquist_mode, int rank, int nranks)
+{
+    ShardGeom g{};
+    const int rows = gg.rows, cols = gg.cols;
+    // Overlap-save unless the Nyquist quirk of pffft is asked for (it is defined on the
+    // reference's full-length tile) or the kernel is too wide for the block menu.
+    int want_ols = nyquist_mode == 0 ? 1 : 0;
+    if (const char* e = std::getenv("BLUR_B200_ALGO")) {
+        if (!std::strcmp(e, "full")) want_ols = 0;
+    }
+    int force_r0 = 0;
+    if (const char* e = std::getenv("BLUR_B200_OLS_R0")) force_r0 = std::atoi(e);
+    if (want_ols && choose_ols_axis(cols, gg.pad, 1, 32, g.ols_row, force_r0) &&
+        choose_ols_axis(rows, gg.pad, 1, 24, g.ols_col, force_r0))
+        g.algo = 1;
+    const int cp_total = (cols + 1) / 2;
+    int sr = (rows + nranks - 1) / nranks;
+    if (g.algo == 1) {
+        g.cpp = 4 * ((((cols + 7) / 8) + nranks - 1) / nranks);     // whole column octets per rank
+        g.qpitch = g.cpart = 2 * g.cpp;
+    } else {
+        g.cpp = (cp_total + nranks - 1) / nranks;
+    }
+    sr += sr & 1;        // stripes start on even rows: the same row pairs share an FFT for every nranks
+    g.stripe_rows = sr;
+    g.row0 = rank * sr;
+    g.valid_rows = std::max(0, std::min(sr, rows - g.row0));
+    g.valid_ncp = std::max(0, std::min(g.cpp, cp_total - rank * g.cpp));
+    g.block_floats = static_cast<size_t>(3) * g.cpp * sr * 2;
+    return g;
 }
 
 // twA[(q-1)*256 + t] = exp(-2 pi i q t / L), q = 1..R0-1, t < 256

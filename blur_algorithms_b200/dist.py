@@ -5,13 +5,15 @@ reference's flip_block, Source.cpp:540), column pass on column stripes.  One pro
 torch.distributed for the exchange (NCCL over NVLink on GPUs; gloo in the CPU tests, where the two
 passes are supplied by the test as callables).
 
-Layout contract (include/blur_b200.h, blur_io.cuh):
-    row pass writes   q_send [nranks][3][cpp][stripe_rows][2]   block p is for rank p
-    all-to-all gives  q_recv [nranks][3][cpp][stripe_rows][2]   block s came from rank s
-    col pass reads q_recv and writes this rank's column stripe  [rows][2*cpp][3] uint8
+Layout contract (blur_b200_gauss_shard_geometry in include/blur_b200.h):
+    algorithm 0 (full-length FFT per line)   q_send [nranks][3][cpp][stripe_rows][2]
+    algorithm 1 (overlap-save)               q_send [3][nranks][stripe_rows][2*cpp]
+block p of the sender goes to rank p and lands as block `rank` there; the column pass writes this
+rank's column stripe [rows][2*cpp][3] uint8.
 """
 from __future__ import annotations
 
+import ctypes as C
 from dataclasses import dataclass
 
 import torch
@@ -20,53 +22,49 @@ import torch.distributed as dist
 
 @dataclass
 class ShardGeometry:
+    """Mirror of blur_b200_gauss_shard_geometry (host-only C call: the C side is the single
+    source of truth for how the image is cut and which algorithm runs)."""
     rows: int
     cols: int
     nranks: int
     rank: int
+    sigma: float = 1.0
+    nyquist_mode: int = 0
 
-    @property
-    def stripe_rows(self) -> int:
-        sr = -(-self.rows // self.nranks)
-        return sr + (sr & 1)
-
-    @property
-    def cpp(self) -> int:
-        return -(-((self.cols + 1) // 2) // self.nranks)
-
-    @property
-    def row0(self) -> int:
-        return self.rank * self.stripe_rows
-
-    @property
-    def valid_rows(self) -> int:
-        return max(0, min(self.stripe_rows, self.rows - self.row0))
+    def __post_init__(self):
+        from ._lib import check, lib
+        o = (C.c_int64 * 8)()
+        check(lib.blur_b200_gauss_shard_geometry(self.rows, self.cols, float(self.sigma), self.nyquist_mode,
+                                                 self.rank, self.nranks, o))
+        (self.algo, self.stripe_rows, self.cpp, self.row0, self.valid_rows, self.valid_cols,
+         self.block_floats, self.qpitch) = (int(v) for v in o)
 
     @property
     def col0(self) -> int:
         return 2 * self.cpp * self.rank
 
-    @property
-    def valid_cols(self) -> int:
-        return max(0, min(2 * self.cpp, self.cols - self.col0))
 
-    @property
-    def block_floats(self) -> int:
-        return 3 * self.cpp * self.stripe_rows * 2
-
-
-def exchange(q_send: torch.Tensor, q_recv: torch.Tensor, group=None) -> None:
-    """All-to-all of equal blocks: block p of q_send goes to rank p, lands as block `rank` there."""
-    n = dist.get_world_size(group)
+def exchange(q_send: torch.Tensor, q_recv: torch.Tensor, group=None, algo: int = 0) -> None:
+    """All-to-all of equal blocks: block p of q_send goes to rank p, lands as block `rank` there.
+    algo 1 keeps the three channels outermost, so it is one all-to-all per channel."""
+    n = dist.get_world_size(group) if dist.is_initialized() else 1
     if n == 1:
         q_recv.copy_(q_send)
         return
+    if algo == 1:
+        for s, r in zip(q_send.view(3, -1), q_recv.view(3, -1)):
+            _all_to_all(s, r, n, group)
+    else:
+        _all_to_all(q_send.view(-1), q_recv.view(-1), n, group)
+
+
+def _all_to_all(send: torch.Tensor, recv: torch.Tensor, n: int, group) -> None:
     try:
-        dist.all_to_all_single(q_recv.view(-1), q_send.view(-1), group=group)
+        dist.all_to_all_single(recv, send, group=group)
     except (RuntimeError, NotImplementedError):
         # backends without alltoall (older gloo): pairwise exchange
         rank = dist.get_rank(group)
-        s, r = q_send.view(n, -1), q_recv.view(n, -1)
+        s, r = send.view(n, -1), recv.view(n, -1)
         r[rank].copy_(s[rank])
         reqs = []
         for p in range(n):
@@ -87,7 +85,7 @@ class ShardedGaussBlur:
         self.group = group
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.nranks = dist.get_world_size(group) if dist.is_initialized() else 1
-        self.geom = ShardGeometry(rows, cols, self.nranks, self.rank)
+        self.geom = ShardGeometry(rows, cols, self.nranks, self.rank, sigma, nyquist_mode)
         self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
         g = self.geom
         self.q_send = torch.zeros(self.nranks * g.block_floats, dtype=torch.float32, device=self.device)
@@ -107,6 +105,6 @@ class ShardedGaussBlur:
         stripe of the result, uint8 [rows, valid_cols, 3] (a view into an internal buffer)."""
         if self.geom.valid_rows > 0:
             self._row_pass(in_stripe, self.q_send)
-        exchange(self.q_send, self.q_recv, self.group)
+        exchange(self.q_send, self.q_recv, self.group, self.geom.algo)
         self._col_pass(self.q_recv, self.out_cols)
         return self.out_cols[:, : self.geom.valid_cols]

@@ -82,6 +82,17 @@ void blur_b200_gauss_plan_destroy(blur_b200_plan *plan);
  * [21],[22]=blocks per line [23]=row quads per stripe */
 int blur_b200_gauss_plan_info(const blur_b200_plan *plan, int64_t info[24]);
 
+/* Host-only (no GPU needed): how a rows x cols image is cut over `nranks` GPUs and which
+ * algorithm the plan will use.  out[0]=algorithm (0 full-length FFT per line, 1 overlap-save)
+ * [1]=stripe_rows [2]=cpp (column pairs per rank) [3]=rank's first row [4]=rank's valid rows
+ * [5]=rank's valid columns [6]=floats per (stripe,part) block of Q [7]=Q row pitch (algorithm 1).
+ * Q layout exchanged between the passes (block p of the sender goes to rank p):
+ *   algorithm 0: float [nranks][3][cpp][stripe_rows][2]           one all-to-all
+ *   algorithm 1: float [3][nranks][stripe_rows][2*cpp]            one all-to-all per channel
+ * (the reference's `resf` + flip_block, Source.cpp:536,540). */
+int blur_b200_gauss_shard_geometry(int rows, int cols, double sigma, int nyquist_mode, int rank, int nranks,
+                                   int64_t out[8]);
+
 /* Whole blur, device resident: d_in and d_out are uint8 [rows][cols][3]; may alias (in place,
  * like image.data in the reference). */
 int blur_b200_gauss_run_device(blur_b200_plan *plan, const uint8_t *d_in, uint8_t *d_out, void *stream);
@@ -95,8 +106,9 @@ int blur_b200_gauss_u8c3(uint8_t *h_bgr, int rows, int cols, double sigma, int n
 
 /* Pieces of the sharded pipeline (single-GPU plans accept them too, with nranks = 1):
  *   row pass : d_in_stripe = this rank's rows of the image (uint8 [valid rows][cols][3])
- *              d_q         = float [nranks][3][cpp][stripe_rows][2]  (block p goes to rank p)
- *   col pass : d_q_chunks  = float [nranks][3][cpp][stripe_rows][2]  (block s came from rank s)
+ *              d_q         = nranks * info[8] floats in the layout of blur_b200_gauss_shard_geometry
+ *                            (zero it once before the first call: padding columns are never written)
+ *   col pass : d_q_chunks  = the same layout after the exchange (block s came from rank s)
  *              d_out_cols  = uint8 [rows][2*cpp][3]  this rank's column stripe of the result */
 int blur_b200_gauss_row_pass(blur_b200_plan *plan, const uint8_t *d_in_stripe, float *d_q, void *stream);
 int blur_b200_gauss_col_pass(blur_b200_plan *plan, const float *d_q_chunks, uint8_t *d_out_cols, void *stream);

@@ -10,6 +10,7 @@
 #include "../../blur_algorithms_b200/csrc/fft_plan.hpp"
 #include "../../blur_algorithms_b200/csrc/blur_io.cuh"
 #include "../../blur_algorithms_b200/csrc/fft_dispatch.cuh"
+#include "../../blur_algorithms_b200/csrc/ols_plan.hpp"
 
 using namespace blurb200;
 
@@ -43,7 +44,165 @@ static void run_units(const FftGeom& g, const IO& io, const std::vector<float2>&
     }
 }
 
+// ---- overlap-save path (ols_core.cuh) -----------------------------------------------------------
+#define OLS_R0_SWITCH(r, F)                                                                         \
+    switch (r) {                                                                                    \
+        case 4: F(4); break;   case 6: F(6); break;   case 8: F(8); break;   case 12: F(12); break; \
+        case 16: F(16); break; case 24: F(24); break; case 32: F(32); break;                        \
+        default: break;                                                                             \
+    }
+
+struct OlsTables {
+    std::vector<float2> twA, twB;
+    std::vector<float> kt;
+    OlsTables(int R0, double sigma, int ksize)
+    {
+        make_ols_twiddles_a(R0, twA);
+        make_ols_twiddles_b(twB);
+        make_ols_kt(R0, sigma, ksize, kt);
+    }
+};
+
+template <int R0>
+static void ols_row_units(const OlsRowIO& io, const OlsTables& T)
+{
+#pragma omp parallel
+    {
+        std::vector<float2> smem(static_cast<size_t>(256) * R0);
+        float2* s = smem.data();
+#pragma omp for schedule(dynamic, 4)
+        for (int unit = 0; unit < io.nunits; ++unit) {
+            const OlsRowIO::Ctx ctx = io.begin(unit);
+            for (int t = 0; t < 256; ++t) ols_pass_a_fwd<R0, 1>(s, s, 0, t, T.twA.data(), io, ctx);
+            for (int it = 0; it < 16 * R0; ++it) ols_pass_b<false, 1>(s, it, T.twB.data());
+            for (int it = 0; it < 16 * R0; ++it) ols_mid<R0, 1>(s, it, T.kt.data());
+            for (int it = 0; it < 16 * R0; ++it) ols_pass_b<true, 1>(s, it, T.twB.data());
+            for (int t = 0; t < 256; ++t) ols_pass_a_inv<R0, 1>(s, 0, t, T.twA.data(), io, ctx);
+        }
+    }
+}
+
+// q = Q as received: [3][rows_total][qpitch]
+template <int R0>
+static void ols_col_units(const OlsColIO& io, const float* q, int qpitch, int rows_total, const OlsTables& T)
+{
+    constexpr int F = 4, L = 256 * R0;
+#pragma omp parallel
+    {
+        std::vector<float2> smem(static_cast<size_t>(F) * L), nat(static_cast<size_t>(F) * L);
+#pragma omp for schedule(dynamic, 4)
+        for (int unit = 0; unit < io.nunits; ++unit) {
+            const OlsColIO::Ctx ctx = io.begin(unit);
+            // what the TMA boxes deliver: rows outside the tensor are zero-filled
+            for (int i = 0; i < L; ++i)
+                for (int X = 0; X < F; ++X) {
+                    const int r = ctx.s + i;
+                    float2 v = make_float2(0.f, 0.f);
+                    if (r >= 0 && r < rows_total) {
+                        const float* p = q + (static_cast<size_t>(ctx.ch) * rows_total + r) * qpitch + ctx.oct * 8 + 2 * X;
+                        v = make_float2(p[0], p[1]);
+                    }
+                    nat[static_cast<size_t>(F) * i + X] = v;
+                }
+            if (!ctx.interior)
+                for (int e = 0; e < F * L; ++e) ols_col_patch(nat.data(), e, ctx.s, io.ax);
+            for (int X = 0; X < F; ++X) {
+                float2* sx = smem.data() + X;
+                for (int t = 0; t < 256; ++t) ols_pass_a_fwd<R0, F>(sx, nat.data() + X, X, t, T.twA.data(), io, ctx);
+                for (int it = 0; it < 16 * R0; ++it) ols_pass_b<false, F>(sx, it, T.twB.data());
+                for (int it = 0; it < 16 * R0; ++it) ols_mid<R0, F>(sx, it, T.kt.data());
+                for (int it = 0; it < 16 * R0; ++it) ols_pass_b<true, F>(sx, it, T.twB.data());
+                for (int t = 0; t < 256; ++t) ols_pass_a_inv<R0, F>(sx, X, t, T.twA.data(), io, ctx);
+            }
+        }
+    }
+}
+
+static int ols_row_pass(const uint8_t* in_stripe, float* q, const GaussGeometry& gg, const ShardGeom& sg, double sigma,
+                        int nranks)
+{
+    if (sg.valid_rows <= 0) return 0;
+    OlsRowIO io{};
+    io.in = in_stripe; io.q = q; io.rows = sg.valid_rows; io.cols = gg.cols; io.npairs = (sg.valid_rows + 1) / 2;
+    io.srows = sg.stripe_rows; io.qpitch = sg.qpitch; io.cpart = sg.cpart; io.nparts = nranks;
+    io.ax = sg.ols_row; io.nunits = io.ax.nblocks * 3 * io.npairs;
+    const OlsTables T(io.ax.R0, sigma, gg.ksize);
+#define F_(R) ols_row_units<R>(io, T)
+    OLS_R0_SWITCH(io.ax.R0, F_)
+#undef F_
+    return 0;
+}
+
+// out_cols: uint8 [rows][2*cpp][3] (this rank's column stripe)
+static int ols_col_pass(const float* q_recv, uint8_t* out_cols, const GaussGeometry& gg, const ShardGeom& sg, double sigma,
+                        int rank, int nranks)
+{
+    const int rows = gg.rows;
+    OlsColIO io{};
+    io.noct = std::min(sg.qpitch / 8, (std::max(0, gg.cols - rank * sg.cpart) + 7) / 8);
+    if (io.noct <= 0) return 0;
+    std::vector<uint8_t> U(static_cast<size_t>(3) * io.noct * rows * 8);
+    io.u = U.data(); io.rows = rows; io.ax = sg.ols_col; io.nunits = io.ax.nblocks * 3 * io.noct;
+    const OlsTables T(io.ax.R0, sigma, gg.ksize);
+#define F_(R) ols_col_units<R>(io, q_recv, sg.qpitch, nranks * sg.stripe_rows, T)
+    OLS_R0_SWITCH(io.ax.R0, F_)
+#undef F_
+    for (int r = 0; r < rows; ++r)
+        for (int c = 0; c < io.noct * 8 && c < 2 * sg.cpp; ++c)
+            for (int ch = 0; ch < 3; ++ch)
+                out_cols[(static_cast<size_t>(r) * 2 * sg.cpp + c) * 3 + ch] =
+                    U[((static_cast<size_t>(ch) * io.noct + (c >> 3)) * rows + r) * 8 + (c & 7)];
+    return 0;
+}
+
 extern "C" {
+
+// Overlap-save Gaussian path on the CPU through the device code, cut over `nparts` emulated
+// ranks (row stripes -> exchange by copies -> column stripes).  Returns 0, or 4 if the plan would
+// not pick the overlap-save algorithm.  info: [0]=L_row [1]=L_col [2]=nblocks_row [3]=nblocks_col
+int emul_ols_gauss(const uint8_t* in, uint8_t* out, int rows, int cols, double sigma, int nparts, float* rowpass_planar,
+                   int* info)
+{
+    const GaussGeometry gg = gauss_geometry(rows, cols, sigma);
+    if (gg.pad < 0 || gg.pad > rows - 1 || gg.pad > cols - 1) return 2;
+    const int P = nparts;
+    std::vector<ShardGeom> sg;
+    for (int r = 0; r < P; ++r) sg.push_back(shard_geometry(gg, 0, r, P));
+    if (sg[0].algo != 1) return 4;
+    if (info) { info[0] = sg[0].ols_row.L; info[1] = sg[0].ols_col.L; info[2] = sg[0].ols_row.nblocks; info[3] = sg[0].ols_col.nblocks; }
+    const size_t bf = sg[0].block_floats, chf = bf / 3;      // floats per (stripe, part) block / per channel of it
+    std::vector<std::vector<float>> send(P, std::vector<float>(bf * P, 0.f));
+    for (int r = 0; r < P; ++r)
+        ols_row_pass(in + static_cast<size_t>(sg[r].row0) * cols * 3, send[r].data(), gg, sg[r], sigma, P);
+    if (rowpass_planar)
+        for (int s = 0; s < P; ++s)
+            for (int ch = 0; ch < 3; ++ch)
+                for (int r = 0; r < sg[s].valid_rows; ++r)
+                    for (int x = 0; x < cols; ++x) {
+                        const int part = x / sg[s].cpart, xl = x - part * sg[s].cpart;
+                        rowpass_planar[(static_cast<size_t>(ch) * rows + sg[s].row0 + r) * cols + x] =
+                            send[s][((static_cast<size_t>(ch) * P + part) * sg[s].stripe_rows + r) * sg[s].qpitch + xl];
+                    }
+    for (int p = 0; p < P; ++p) {
+        // "all-to-all per channel": recv[ch][src] = send[src][ch][p]
+        std::vector<float> recv(bf * P);
+        for (int ch = 0; ch < 3; ++ch)
+            for (int s = 0; s < P; ++s)
+                std::copy(send[s].begin() + (static_cast<size_t>(ch) * P + p) * chf,
+                          send[s].begin() + (static_cast<size_t>(ch) * P + p + 1) * chf,
+                          recv.begin() + (static_cast<size_t>(ch) * P + s) * chf);
+        std::vector<uint8_t> oc(static_cast<size_t>(rows) * 2 * sg[p].cpp * 3, 0);
+        ols_col_pass(recv.data(), oc.data(), gg, sg[p], sigma, p, P);
+        for (int r = 0; r < rows; ++r)
+            for (int c = 0; c < 2 * sg[p].cpp; ++c) {
+                const int x = p * 2 * sg[p].cpp + c;
+                if (x >= cols) continue;
+                for (int ch = 0; ch < 3; ++ch)
+                    out[(static_cast<size_t>(r) * cols + x) * 3 + ch] = oc[(static_cast<size_t>(r) * 2 * sg[p].cpp + c) * 3 + ch];
+            }
+    }
+    return 0;
+}
 
 // Gaussian 1-D tile path on the CPU through the device code.  nparts > 1 exercises the
 // multi-GPU Q layout (row stripes x column-pair parts) inside one process.
@@ -129,6 +288,10 @@ int emul_row_pass(const uint8_t* in_stripe, float* q, int rows, int cols, double
                   int rank, int nranks)
 {
     const GaussGeometry gg = gauss_geometry(rows, cols, sigma);
+    {
+        const ShardGeom sg = shard_geometry(gg, nyquist_mode, rank, nranks);
+        if (sg.algo == 1) return ols_row_pass(in_stripe, q, gg, sg, sigma, nranks);
+    }
     FftGeom grow;
     if (!make_geom(gg.n_row, grow)) return 3;
     std::vector<float2> tw; make_twiddles(grow.N, tw);
@@ -149,6 +312,10 @@ int emul_col_pass(const float* q_chunks, uint8_t* out_cols, int rows, int cols, 
                   int rank, int nranks)
 {
     const GaussGeometry gg = gauss_geometry(rows, cols, sigma);
+    {
+        const ShardGeom sg = shard_geometry(gg, nyquist_mode, rank, nranks);
+        if (sg.algo == 1) return ols_col_pass(q_chunks, out_cols, gg, sg, sigma, rank, nranks);
+    }
     FftGeom gcol;
     if (!make_geom(gg.n_col, gcol)) return 3;
     std::vector<float2> tw; make_twiddles(gcol.N, tw);

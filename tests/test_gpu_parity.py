@@ -130,7 +130,11 @@ def test_gauss_sharded_emulated_on_one_gpu(bb, torch):
                 pl.row_pass(d_img[pl.info["row0"]:pl.info["row0"] + pl.info["valid_rows"]].contiguous(), send[r])
         outs = []
         for r, pl in enumerate(plans):
-            recv = torch.cat([send[s][r * bf:(r + 1) * bf] for s in range(P)])
+            if pl.info["algo"] == 1:     # [3][nranks][...]: one exchange per channel
+                chf = bf // 3
+                recv = torch.cat([send[s].view(3, P, chf)[ch, r] for ch in range(3) for s in range(P)])
+            else:
+                recv = torch.cat([send[s][r * bf:(r + 1) * bf] for s in range(P)])
             oc = torch.zeros((rows, 2 * pl.info["cpp"], 3), dtype=torch.uint8, device="cuda")
             pl.col_pass(recv, oc)
             outs.append(oc)

@@ -99,6 +99,36 @@ def test_device_code_on_cpu_matches_oracle(emu, oracle, rows, cols, sigma):
             assert np.abs(out.astype(int) - ref.astype(int)).max() <= 1   # +-1 LSB
 
 
+@pytest.mark.parametrize("rows,cols,sigma", [(64, 96, 2.0), (100, 75, 3.0), (135, 241, 6.0), (240, 320, 5.0),
+                                             (467, 700, 7.5), (300, 1300, 25.0), (1100, 90, 12.0)])
+def test_overlap_save_device_code_on_cpu_matches_oracle(emu, oracle, rows, cols, sigma):
+    """ols_core.cuh (the default algorithm for nyquist_mode 0) executed on the CPU: blocks,
+    reflect patching, swizzled passes, planar Q, octet U, and the multi-rank cut."""
+    img = synth("noise", rows, cols, 5)
+    ref, rp, _ = oracle.gauss_blur_1d(img, sigma, 0, want_f32=True)
+    single = None
+    for nparts in (1, 2, 3):
+        out, erp, info = emu.ols_gauss(img, sigma, nparts)
+        assert np.abs(erp - rp).max() <= 255 * 1e-5          # float32 intermediate, 1e-5 relative
+        assert np.abs(out.astype(int) - ref.astype(int)).max() <= 1   # +-1 LSB
+        single = out if single is None else single
+        assert np.array_equal(out, single)                   # the cut never changes a bit
+
+
+def test_overlap_save_multi_block_lines(emu, oracle, monkeypatch):
+    """Force the smallest block (L = 1024) so that lines span several blocks with both edge and
+    interior blocks, and an odd width / height."""
+    monkeypatch.setenv("BLUR_B200_OLS_R0", "4")
+    for rows, cols, sigma in [(1500, 37, 4.0), (45, 2300, 9.0), (1201, 1111, 20.0)]:
+        img = synth("noise", rows, cols, 11)
+        ref = oracle.gauss_blur_1d(img, sigma, 0)
+        out, _, info = emu.ols_gauss(img, sigma, 1)
+        assert info[0] == 1024 and info[1] == 1024 and max(info[2], info[3]) >= 2
+        assert np.abs(out.astype(int) - ref.astype(int)).max() <= 1, (rows, cols)
+    out, _, _ = emu.ols_gauss(synth("const", 1300, 40), 3.0, 1)
+    assert np.all(out == 200)
+
+
 def test_device_code_edge_inputs(emu, oracle):
     for kind in ("const", "impulse", "stripes", "ramp"):
         img = synth(kind, 96, 128)
@@ -134,7 +164,7 @@ for rows, cols, sigma, mode in [(64, 96, 2.0, 0), (135, 241, 6.0, 1), (101, 75, 
     parts = [torch.zeros((rows, 2 * g.cpp, 3), dtype=torch.uint8) for _ in range(n)]
     dist.all_gather(parts, sb.out_cols)
     full = torch.cat(parts, 1)[:, :cols].numpy()
-    single, _, _, _ = emu.gauss(img, sigma, mode, 1)
+    single = emu.ols_gauss(img, sigma, 1)[0] if g.algo == 1 else emu.gauss(img, sigma, mode, 1)[0]
     assert np.array_equal(full, single), (rows, cols)
     ref = Oracle().gauss_blur_1d(img, sigma, mode)
     assert np.abs(full.astype(int) - ref.astype(int)).max() <= 1

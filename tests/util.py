@@ -85,7 +85,8 @@ class Emulator:
         so = os.path.join(HERE, "emul", "libemul.so")
         src = os.path.join(HERE, "emul", "emulate.cpp")
         csrc = os.path.join(os.path.dirname(HERE), "blur_algorithms_b200", "csrc")
-        deps = [src] + [os.path.join(csrc, f) for f in ("fft_core.cuh", "fft_plan.hpp", "blur_io.cuh", "dft_codelets.cuh")]
+        deps = [src] + [os.path.join(csrc, f) for f in ("fft_core.cuh", "fft_plan.hpp", "blur_io.cuh", "dft_codelets.cuh", "ols_core.cuh", "ols_plan.hpp",
+                                                           "dft_codelets2.cuh", "cplx2.cuh")]
         if not os.path.exists(so) or any(os.path.getmtime(d) > os.path.getmtime(so) for d in deps if os.path.exists(d)):
             subprocess.run(["g++", "-O2", "-std=c++17", "-fopenmp", "-fPIC", "-shared", "-o", so, src], check=True)
         L = self.lib = C.CDLL(so)
@@ -94,6 +95,7 @@ class Emulator:
         i32p = np.ctypeslib.ndpointer(np.int32, flags="C")
         L.emul_fft_roundtrip.argtypes = [C.c_int, f32p, f32p, f32p, f32p, f32p, f32p]
         L.emul_gauss.argtypes = [u8p, u8p, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, C.c_void_p, i32p, i32p]
+        L.emul_ols_gauss.argtypes = [u8p, u8p, C.c_int, C.c_int, C.c_double, C.c_int, C.c_void_p, i32p]
         L.emul_row_pass.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int]
         L.emul_col_pass.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_int, C.c_int, C.c_int]
 
@@ -106,6 +108,17 @@ class Emulator:
                                    nparts, rp.ctypes.data, rr, rc)
         assert code == 0, code
         return out, rp, rr, rc
+
+    def ols_gauss(self, img, sigma, nparts=1):
+        """overlap-save path (the plan's default for nyquist_mode 0); returns (out, rowpass, info)"""
+        rows, cols = img.shape[:2]
+        out = np.zeros_like(img)
+        rp = np.zeros((3, rows, cols), np.float32)
+        info = np.zeros(4, np.int32)
+        code = self.lib.emul_ols_gauss(np.ascontiguousarray(img).reshape(-1), out.reshape(-1), rows, cols, sigma,
+                                       nparts, rp.ctypes.data, info)
+        assert code == 0, code
+        return out, rp, info
 
     def fft_roundtrip(self, a, b):
         N = a.size
