@@ -93,49 +93,65 @@ __global__ void q_to_planar_kernel(const float* __restrict__ q, float* __restric
         q[((static_cast<size_t>(part * 3 + ch) * cpp + cpl) * qrows + r) * 2 + (x & 1)];
 }
 
-// overlap-save U [3][noct][rows][8] (uint8) -> out [rows][out_cols][3].  Tile = 64 rows x 4 octets
-// (32 columns): 12 runs of 512 contiguous bytes in, 64 runs of 96 contiguous bytes out.
-// Replaces the reference's second flip_block (Source.cpp:562) and interleave_BGR (:567).
-constexpr int kOctTileR = 64;
+// overlap-save U [3][noct][rows][8] (uint8) -> out [rows][out_cols][3].  Replaces the reference's
+// second flip_block (Source.cpp:562) and interleave_BGR (:567).  No shared memory: a thread owns
+// 4 image rows x 16 columns (two octets).  Per channel and octet its four rows are one 32-byte
+// sector of U (two 128-bit loads); the 48 output bytes of each row are assembled with byte
+// permutes and leave as three 128-bit stores, the lanes of a warp covering 1536 contiguous bytes.
+__device__ __forceinline__ void il_octet(uint32_t b, uint32_t g, uint32_t r, uint32_t& w0, uint32_t& w1, uint32_t& w2)
+{
+    w0 = __byte_perm(__byte_perm(b, g, 0x1040), r, 0x3410);     // b0 g0 r0 b1
+    w1 = __byte_perm(__byte_perm(g, b, 0x2601), r, 0x3250);     // g1 r1 b2 g2
+    w2 = __byte_perm(__byte_perm(r, b, 0x3072), g, 0x3710);     // r2 b3 g3 r3
+}
+
 __global__ void __launch_bounds__(256)
 interleave_oct_kernel(const uint8_t* __restrict__ u, uint8_t* __restrict__ out, int rows, int noct,
                       int ncols /* valid columns to emit */, int out_cols /* row pitch of out, in pixels */, int vec)
 {
-    __shared__ __align__(8) uint8_t tile[3][4][kOctTileR][8];       // 6 KB
-    const int o0 = blockIdx.x * 4, r0 = blockIdx.y * kOctTileR;
-    const int tid = threadIdx.x;
-    for (int i = tid; i < 12 * kOctTileR; i += 256) {
-        const int line = i / kOctTileR, r = i - line * kOctTileR;
-        const int ch = line >> 2, o = line & 3;
-        if (o0 + o < noct && r0 + r < rows)
-            *reinterpret_cast<uint2*>(&tile[ch][o][r][0]) =
-                *reinterpret_cast<const uint2*>(u + ((static_cast<size_t>(ch) * noct + o0 + o) * rows + r0 + r) * 8);
-    }
-    __syncthreads();
-    const int c0 = o0 * 8;
-    const int nc = min(32, ncols - c0);
-    if (nc <= 0) return;
-    if (vec && nc == 32) {
-        for (int i = tid; i < kOctTileR * 24; i += 256) {
-            const int r = i / 24, w = i - r * 24;
-            if (r0 + r >= rows) continue;
-            uint32_t v = 0;
+    const int op = blockIdx.x * 32 + threadIdx.x;          // octet pair
+    const int r0 = (blockIdx.y * 8 + threadIdx.y) * 4;     // first of 4 rows
+    const int c0 = op * 16;
+    if (c0 >= ncols || r0 >= rows) return;
+    if (vec && c0 + 16 <= ncols && r0 + 4 <= rows) {
+        uint4 v[3][2][2];                                   // [channel][octet][row pair]: x,y = row 2k, z,w = row 2k+1
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const int b = 4 * w + k, c = b / 3, ch = b - c * 3;
-                v |= static_cast<uint32_t>(tile[ch][c >> 3][r][c & 7]) << (8 * k);
+        for (int ch = 0; ch < 3; ++ch)
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const uint4* p = reinterpret_cast<const uint4*>(u + ((static_cast<size_t>(ch) * noct + 2 * op + e) * rows + r0) * 8);
+                v[ch][e][0] = __ldg(p);
+                v[ch][e][1] = __ldg(p + 1);
             }
-            *reinterpret_cast<uint32_t*>(out + (static_cast<size_t>(r0 + r) * out_cols + c0) * 3 + 4 * w) = v;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            uint32_t w[12];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const uint4 B = v[0][e][k >> 1], G = v[1][e][k >> 1], R = v[2][e][k >> 1];
+                const uint32_t blo = (k & 1) ? B.z : B.x, bhi = (k & 1) ? B.w : B.y;
+                const uint32_t glo = (k & 1) ? G.z : G.x, ghi = (k & 1) ? G.w : G.y;
+                const uint32_t rlo = (k & 1) ? R.z : R.x, rhi = (k & 1) ? R.w : R.y;
+                il_octet(blo, glo, rlo, w[6 * e + 0], w[6 * e + 1], w[6 * e + 2]);
+                il_octet(bhi, ghi, rhi, w[6 * e + 3], w[6 * e + 4], w[6 * e + 5]);
+            }
+            uint4* d = reinterpret_cast<uint4*>(out + (static_cast<size_t>(r0 + k) * out_cols + c0) * 3);
+            d[0] = make_uint4(w[0], w[1], w[2], w[3]);
+            d[1] = make_uint4(w[4], w[5], w[6], w[7]);
+            d[2] = make_uint4(w[8], w[9], w[10], w[11]);
         }
-    } else {
-        const int nbytes = nc * 3;
-        for (int i = tid; i < kOctTileR * 96; i += 256) {
-            const int r = i / 96, b = i - r * 96;
-            if (b >= nbytes || r0 + r >= rows) continue;
-            const int c = b / 3, ch = b - c * 3;
-            out[(static_cast<size_t>(r0 + r) * out_cols + c0) * 3 + b] = tile[ch][c >> 3][r][c & 7];
-        }
+        return;
     }
+    // ragged edge / unaligned pitch: byte by byte
+    for (int k = 0; k < 4 && r0 + k < rows; ++k)
+        for (int e = 0; e < 2 && 2 * op + e < noct; ++e)
+            for (int px = 0; px < 8; ++px) {
+                const int c = c0 + 8 * e + px;
+                if (c >= ncols) break;
+                for (int ch = 0; ch < 3; ++ch)
+                    out[(static_cast<size_t>(r0 + k) * out_cols + c) * 3 + ch] =
+                        u[((static_cast<size_t>(ch) * noct + 2 * op + e) * rows + r0 + k) * 8 + px];
+            }
 }
 
 // overlap-save Q [3][nparts][srows][qpitch] -> planar float [3][rows][cols]   (parity hook only)
@@ -486,7 +502,7 @@ int run_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, float* d_q, cuda
         io.npairs = cdiv(p->valid_rows, 2);
         io.srows = p->stripe_rows; io.qpitch = p->qpitch; io.cpart = p->cpart; io.nparts = p->nranks;
         io.ax = p->ols_row;
-        io.nunits = io.ax.nblocks * 3 * io.npairs;
+        io.nunits = io.ax.nblocks * io.npairs;
         CU_TRY(launch_ols_row(io, p->d_ols_twa_row, p->d_ols_twb, p->d_ols_kt_row, p->num_sms, st));
         ++g_launches;
         return BLUR_B200_OK;
@@ -537,9 +553,10 @@ int run_interleave(blur_b200_plan* p, uint8_t* d_out, int ncols, int out_cols, c
     if (ncols <= 0) return BLUR_B200_OK;
     if (p->algo == 1) {
         const int noct = std::min(p->qpitch / 8, cdiv(std::max(0, p->cols - p->rank * p->cpart), 8));
-        const int vec = (static_cast<size_t>(out_cols) * 3 % 4 == 0) && (reinterpret_cast<uintptr_t>(d_out) % 4 == 0);
-        dim3 g(cdiv(noct, 4), cdiv(p->rows, kOctTileR));
-        interleave_oct_kernel<<<g, 256, 0, st>>>(p->d_u, d_out, p->rows, noct, std::min(ncols, noct * 8), out_cols, vec);
+        const int vec = (static_cast<size_t>(out_cols) * 3 % 16 == 0) && (reinterpret_cast<uintptr_t>(d_out) % 16 == 0) &&
+                        (reinterpret_cast<uintptr_t>(p->d_u) % 32 == 0) && (p->rows % 4 == 0);
+        dim3 g(cdiv(cdiv(noct, 2), 32), cdiv(cdiv(p->rows, 4), 8));
+        interleave_oct_kernel<<<g, dim3(32, 8), 0, st>>>(p->d_u, d_out, p->rows, noct, std::min(ncols, noct * 8), out_cols, vec);
         CU_TRY(cudaGetLastError());
         ++g_launches;
         return BLUR_B200_OK;

@@ -27,6 +27,19 @@ static inline float2 make_float2(float a, float b) { float2 r; r.x = a; r.y = b;
 
 namespace blurb200 {
 
+// store one complex value as a single 64-bit access.  (A plain `*p = v` makes ptxas copy the
+// register pair before every STS.64.)
+BLUR_HD void cstore(float2* p, float2 v)
+{
+#ifdef __CUDA_ARCH__
+    unsigned long long u;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(u) : "f"(v.x), "f"(v.y));
+    asm volatile("st.shared.b64 [%0], %1;" ::"r"(static_cast<unsigned>(__cvta_generic_to_shared(p))), "l"(u) : "memory");
+#else
+    *p = v;
+#endif
+}
+
 // a + b
 BLUR_HD float2 cadd(float2 a, float2 b)
 {

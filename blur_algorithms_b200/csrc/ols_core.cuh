@@ -25,19 +25,17 @@
 // Forward = decimation in frequency, so the spectrum is in digit-reversed order at `mid`; the
 // multiplier table is stored in that order (the reference README's "unordered layout" idea).
 //
-// Shared-memory layout: F transforms (F = 1, 2 or 4) are interleaved element-wise and logical
-// element p of transform X lives at slot F*(p ^ ((p >> 4) & M)) + X with M = 16/F - 1.  The XOR
-// only touches the low bits, so
-//   pass A : slot = F*(256*q + (t ^ (t>>4 & M))) + X        one XOR per item, immediates after that
-//   pass B : slot = F*(256*k0 + 16*j + (t ^ (j & M))) + X
-//   mid    : slot = F*(16*u + (j ^ (u & M))) + X
-// Work item i of a pass is (X = i % F, index = i / F): the 16 lanes of a half-warp then cover 16/F
-// consecutive indices x F transforms = 16 distinct 8-byte bank pairs in every pass: conflict
-// free without padding.  A block that arrives by TMA in NATURAL order F*p + X (column pass: F
-// column pairs = 2F adjacent floats per image row) is consumed by pass A in place: item (X, t)
-// reads slots F*(256*j + t) + X and writes F*(256*q + swz(t)) + X; swz(t) stays inside t's
-// aligned group of 16/F indices, i.e. inside the same half-warp of the same round, whose loads all
-// precede its stores.
+// Shared-memory layout: F transforms (F = 1 or 4) are interleaved element-wise and logical element
+// p of transform X lives at slot F*(p + (p >> 4)) + X: one element of padding after every 16.
+// With p = 256*q + t (pass A), 256*k0 + 16*j + t (pass B) or 16*u + j (mid) the slot is
+//   pass A : F*(272*q + t + (t >> 4)) + X
+//   pass B : F*(272*k0 + 17*j + t) + X
+//   mid    : F*(17*u + j) + X
+// so every access of a work item is its base address plus a compile-time immediate, and a
+// half-warp (16 consecutive work items, 8-byte elements) always covers 16 distinct bank pairs:
+// conflict free in all passes.  Pass A item t reads and writes the same slot set {272*q + pad(t)},
+// and the input block sits in the tile in natural order at the same slots, so pass A is in
+// place per item and a thread may refill "its" slots for the next block without a barrier.
 //
 // All functions are host/device: tests/emul runs them on the CPU.
 #pragma once
@@ -67,7 +65,9 @@ BLUR_HD int ols_src(int g, int len, int pad)
     return g;
 }
 
-template <int F> BLUR_HD int ols_swz(int t) { return t ^ ((t >> 4) & (16 / F - 1)); }
+BLUR_HD int ols_pad(int p) { return p + (p >> 4); }
+// float2 slots of one transform's tile
+BLUR_HD constexpr int ols_tile_slots(int R0) { return 272 * R0; }
 
 // Item t of pass A owns tile indices 256 j + t.  Those inside [halo, halo + nvalid) are j in [jlo, jhi].
 BLUR_HD void ols_item_range(int t, int halo, int nvalid, int& jlo, int& jhi)
@@ -90,24 +90,22 @@ BLUR_HD void ols_item_range(int t, int halo, int nvalid, int& jlo, int& jhi)
 // In all pass functions `sx` = shared-memory base of the CTA's tile + X.
 
 // ---- pass A, forward: item (X, t), t in [0, 256)
-// `nat` = where a kSmemInput block sits in natural order: the kernel passes sx itself (in place,
-// see the layout note above); the sequential CPU emulator passes a copy.
 template <int R0, int F, class IO>
-BLUR_HD void ols_pass_a_fwd(float2* sx, const float2* nat, int X, int t, const float2* __restrict__ twA, const IO& io,
+BLUR_HD void ols_pass_a_fwd(float2* sx, int X, int t, const float2* __restrict__ twA, const IO& io,
                             const typename IO::Ctx& ctx)
 {
     float2 x[R0];
+    float2* base = sx + F * ols_pad(t);
     if (IO::kSmemInput) {
 #pragma unroll
-        for (int j = 0; j < R0; ++j) x[j] = nat[F * (256 * j + t)];
+        for (int j = 0; j < R0; ++j) x[j] = base[F * 272 * j];
     } else {
         io.template load_item<R0>(ctx, X, t, x);
     }
     CDft<R0, false>::run(x);
-    const int ta = ols_swz<F>(t);
-    sx[F * ta] = x[0];
+    cstore(base, x[0]);
 #pragma unroll
-    for (int q = 1; q < R0; ++q) sx[F * (256 * q + ta)] = cmul(x[q], twA[(q - 1) * 256 + t]);
+    for (int q = 1; q < R0; ++q) cstore(base + F * 272 * q, cmul(x[q], twA[(q - 1) * 256 + t]));
 }
 
 // ---- pass A, backward
@@ -116,10 +114,10 @@ BLUR_HD void ols_pass_a_inv(const float2* __restrict__ sx, int X, int t, const f
                             const typename IO::Ctx& ctx)
 {
     float2 x[R0];
-    const int ta = ols_swz<F>(t);
-    x[0] = sx[F * ta];
+    const float2* base = sx + F * ols_pad(t);
+    x[0] = base[0];
 #pragma unroll
-    for (int q = 1; q < R0; ++q) x[q] = cmulc(sx[F * (256 * q + ta)], twA[(q - 1) * 256 + t]);
+    for (int q = 1; q < R0; ++q) x[q] = cmulc(base[F * 272 * q], twA[(q - 1) * 256 + t]);
     CDft<R0, true>::run(x);
     io.template store_item<R0>(ctx, X, t, x);
 }
@@ -128,24 +126,23 @@ BLUR_HD void ols_pass_a_inv(const float2* __restrict__ sx, int X, int t, const f
 template <bool INV, int F>
 BLUR_HD void ols_pass_b(float2* __restrict__ sx, int it, const float2* __restrict__ twB)
 {
-    constexpr int M = 16 / F - 1;
     const int t = it & 15;
-    float2* blk = sx + F * ((it >> 4) << 8);
+    float2* blk = sx + F * (272 * (it >> 4) + t);
     float2 x[16];
     if (!INV) {
 #pragma unroll
-        for (int j = 0; j < 16; ++j) x[j] = blk[F * (16 * j + (t ^ (j & M)))];
+        for (int j = 0; j < 16; ++j) x[j] = blk[F * 17 * j];
         CDft<16, false>::run(x);
-        blk[F * t] = x[0];
+        cstore(blk, x[0]);
 #pragma unroll
-        for (int q = 1; q < 16; ++q) blk[F * (16 * q + (t ^ (q & M)))] = cmul(x[q], twB[(q - 1) * 16 + t]);
+        for (int q = 1; q < 16; ++q) cstore(blk + F * 17 * q, cmul(x[q], twB[(q - 1) * 16 + t]));
     } else {
-        x[0] = blk[F * t];
+        x[0] = blk[0];
 #pragma unroll
-        for (int q = 1; q < 16; ++q) x[q] = cmulc(blk[F * (16 * q + (t ^ (q & M)))], twB[(q - 1) * 16 + t]);
+        for (int q = 1; q < 16; ++q) x[q] = cmulc(blk[F * 17 * q], twB[(q - 1) * 16 + t]);
         CDft<16, true>::run(x);
 #pragma unroll
-        for (int j = 0; j < 16; ++j) blk[F * (16 * j + (t ^ (j & M)))] = x[j];
+        for (int j = 0; j < 16; ++j) cstore(blk + F * 17 * j, x[j]);
     }
 }
 
@@ -154,18 +151,16 @@ BLUR_HD void ols_pass_b(float2* __restrict__ sx, int it, const float2* __restric
 template <int R0, int F>
 BLUR_HD void ols_mid(float2* __restrict__ sx, int u, const float* __restrict__ kt)
 {
-    constexpr int M = 16 / F - 1;
-    const int k1 = u & M;
-    float2* grp = sx + F * 16 * u;
+    float2* grp = sx + F * 17 * u;
     float2 x[16];
 #pragma unroll
-    for (int j = 0; j < 16; ++j) x[j] = grp[F * (j ^ k1)];
+    for (int j = 0; j < 16; ++j) x[j] = grp[F * j];
     CDft<16, false>::run(x);
 #pragma unroll
     for (int q = 0; q < 16; ++q) x[q] = cscale(x[q], kt[q * (16 * R0) + u]);
     CDft<16, true>::run(x);
 #pragma unroll
-    for (int j = 0; j < 16; ++j) grp[F * (j ^ k1)] = x[j];
+    for (int j = 0; j < 16; ++j) cstore(grp + F * j, x[j]);
 }
 
 // ---- row pass IO: uint8 interleaved BGR lines -> Q -------------------------------------------
@@ -174,17 +169,33 @@ BLUR_HD void ols_mid(float2* __restrict__ sx, int u, const float* __restrict__ k
 //   in   uint8 [rows][cols][3]
 //   Q    float [3][nparts][srows][qpitch]     row-pass result, planar row-major = the reference's
 //        `resf` (Source.cpp:536).  Row-pass warps write 128 contiguous bytes per store.  The
-//        reference's flip_block (:540) is replaced by TMA: the column pass pulls, per CTA, an
-//        {8 columns x 256 rows} box, which lands in shared memory as four column-pair sequences
-//        interleaved element-wise — the layout its FFT passes work in.  `part` = destination GPU
-//        of the column (1 on a single GPU), srows = rows per stripe, qpitch = columns per part
-//        rounded up to 8.
+//        reference's flip_block (:540) does not exist: a column-pass CTA pulls an {8 columns x L
+//        rows} strip, one 32-byte sector per image row, by asynchronous copies straight into the
+//        slots its FFT passes work on (four column-pair sequences interleaved element-wise).
+//        `part` = destination GPU of the column (1 on a single GPU), srows = rows per stripe,
+//        qpitch = columns per part rounded up to 8.
 //   U    uint8 [3][noct][rows][8]             column-pass result: per channel and column octet,
 //        8 bytes per image row (rounded with +0.5f truncation, Utils.hpp:204-206)
 //   out  uint8 [rows][cols][3]                interleave_oct_kernel: U -> out (replaces
 //        flip_block :562 + interleave_BGR :567)
 //
-// unit = (block * 3 + ch) * npairs + pair ; lines (2*pair, 2*pair + 1) of the stripe.
+// unit = block * npairs + pair ; lines (2*pair, 2*pair + 1) of the stripe, all three channels.
+//
+// The interleaved bytes of the unit's two lines (the block's window of L pixels, 3 bytes each)
+// are staged ONCE in shared memory by 128-bit asynchronous copies (cp.async; deinterleave_BGR of
+// Utils.hpp:159-184 fused into the load) and then read three times, once per channel, by pass A.
+// The copies of the next unit are issued as soon as the last channel has consumed the bytes and
+// complete underneath that channel's remaining four passes.
+//
+// Staging geometry of one line: source bytes [w0*3, w1*3) of the line, w0 = max(s, 0),
+// w1 = min(s + L, cols), copied in 16-byte vectors starting at the 16-byte boundary at or below
+// the first byte.  The staging row (pitch 3L + 16) is addressed in TILE coordinates: byte
+// (tile index i, channel c) sits at b0 + 3 i + c, with b0 in [0, 16) chosen so that source and
+// destination of the copy are congruent mod 16.  For a block that overhangs the line the
+// reflect-101 pixels and the zeros of the reference's tile (Source.cpp:525-529) are then written
+// into the staging row by ols_row_fixup, so pass A reads every block the same way.
+template <int R0> constexpr int ols_raw_pitch() { return 768 * R0 + 16; }
+
 struct OlsRowIO {
     static constexpr bool kSmemInput = false;
     static constexpr int kF = 1;
@@ -197,29 +208,66 @@ struct OlsRowIO {
     int qpitch;            // floats per Q row (columns per part, multiple of 8)
     int cpart;             // image columns per part (multiple of 8 unless nparts == 1)
     int nparts;
-    int nunits;
+    int nunits;            // nblocks * npairs
     OlsAxis ax;            // len = cols
 
+    struct Stage {
+        const uint8_t* src;  // 16-byte aligned global address of the first vector
+        int nvec;            // 16-byte vectors to copy
+        int dst;             // byte offset of the first vector in the staging row (multiple of 16)
+        int b0;              // byte of (tile index 0, channel 0) in the staging row
+    };
     struct Ctx {
-        const uint8_t* pa;   // line a, channel ch, pixel 0
-        float* qa;           // Q float of (ch, part 0, row a, col 0)
+        uint8_t* raw;        // staging area: two rows of ols_raw_pitch<R0>() bytes
+        float* qa;           // Q float of (ch 0, part 0, row a, col 0)
+        int ia, ib;          // byte (tile index i, channel c) of line a / b is raw[ia + 3 i + c] / raw[ib + 3 i + c]
+        int ra;              // first line of the pair
         int s;               // extended-line position of tile index 0
+        int w0, w1;          // staged source pixels [w0, w1)
         int nvalid;          // outputs this block keeps: tile indices [halo, halo + nvalid)
         bool has_b, interior;
     };
-    BLUR_HD Ctx begin(int unit) const
+    BLUR_HD Stage stage_of(int row, int s, int w0, int w1) const
+    {
+        const uint8_t* g = in + (static_cast<size_t>(row) * cols + w0) * 3;
+        const int off = static_cast<int>(reinterpret_cast<uintptr_t>(g) & 15);
+        Stage st;
+        st.src = g - off;
+        st.nvec = (off + (w1 - w0) * 3 + 15) >> 4;
+        const int lead = 3 * (w0 - s);                 // bytes of tile indices before the first staged pixel
+        st.b0 = (off - lead) & 15;
+        st.dst = st.b0 + lead - off;                   // multiple of 16 by construction
+        return st;
+    }
+    BLUR_HD Ctx begin(int unit, uint8_t* raw, int raw_pitch) const
     {
         Ctx c;
-        const int pair = unit % npairs, rest = unit / npairs;
-        const int ch = rest % 3, b = rest / 3;
-        const int ra = 2 * pair;
-        c.has_b = ra + 1 < rows;
-        c.pa = in + static_cast<size_t>(ra) * cols * 3 + ch;
-        c.qa = q + (static_cast<size_t>(ch) * nparts * srows + ra) * qpitch;
+        const int pair = unit % npairs, b = unit / npairs;
+        c.raw = raw;
+        c.ra = 2 * pair;
+        c.has_b = c.ra + 1 < rows;
+        c.qa = q + static_cast<size_t>(c.ra) * qpitch;
         c.s = b * ax.V - ax.halo;
+        c.w0 = c.s < 0 ? 0 : c.s;
+        c.w1 = c.s + ax.L < cols ? c.s + ax.L : cols;
         c.nvalid = cols - b * ax.V < ax.V ? cols - b * ax.V : ax.V;
         c.interior = c.s >= 0 && c.s + ax.L <= cols;
+        c.ia = stage_of(c.ra, c.s, c.w0, c.w1).b0;
+        c.ib = c.has_b ? raw_pitch + stage_of(c.ra + 1, c.s, c.w0, c.w1).b0 : c.ia;
         return c;
+    }
+    // Entry e of the fixup of an edge block: tile index i = e % L of line k = e / L.  Indices whose
+    // extended-line position is outside [0, cols) get the reflect-101 pixel (inside the staged
+    // window) or zeros.
+    BLUR_HD void fixup(const Ctx& c, int e) const
+    {
+        const int k = e >= ax.L ? 1 : 0, i = e - k * ax.L;
+        const int g = c.s + i;
+        if ((g >= 0 && g < cols) || (k && !c.has_b)) return;
+        uint8_t* row = c.raw + (k ? c.ib : c.ia);
+        const int src = ols_src(g, cols, ax.pad);
+#pragma unroll
+        for (int ch = 0; ch < 3; ++ch) row[3 * i + ch] = src < 0 ? 0 : row[3 * (src - c.s) + ch];
     }
     // uint8 -> float without the conversion pipe: 0x4B000000 | b is the float 2^23 + b
     BLUR_HD static float u8f(uint8_t b)
@@ -230,67 +278,61 @@ struct OlsRowIO {
         return static_cast<float>(b);
 #endif
     }
+    // X = channel
     template <int R0>
-    BLUR_HD void load_item(const Ctx& c, int, int t, float2 (&x)[R0]) const
+    BLUR_HD void load_item(const Ctx& c, int X, int t, float2 (&x)[R0]) const
     {
-        const size_t rowb = static_cast<size_t>(cols) * 3;
-        if (c.interior) {
-            const uint8_t* p = c.pa + (c.s + t) * 3;
-            if (c.has_b) {
+        const uint8_t* pa = c.raw + c.ia + 3 * t + X;
+        const int db = c.ib - c.ia;
+        if (c.has_b) {
 #pragma unroll
-                for (int j = 0; j < R0; ++j) x[j] = make_float2(u8f(p[768 * j]), u8f(p[rowb + 768 * j]));
-            } else {
-#pragma unroll
-                for (int j = 0; j < R0; ++j) x[j] = make_float2(u8f(p[768 * j]), 0.f);
-            }
+            for (int j = 0; j < R0; ++j) x[j] = make_float2(u8f(pa[768 * j]), u8f(pa[db + 768 * j]));
         } else {
 #pragma unroll
-            for (int j = 0; j < R0; ++j) {
-                const int g = ols_src(c.s + 256 * j + t, cols, ax.pad);
-                x[j] = make_float2(0.f, 0.f);
-                if (g >= 0) {
-                    const uint8_t* p = c.pa + g * 3;
-                    x[j] = make_float2(u8f(p[0]), c.has_b ? u8f(p[rowb]) : 0.f);
-                }
-            }
+            for (int j = 0; j < R0; ++j) x[j] = make_float2(u8f(pa[768 * j]), 0.f);
         }
     }
     template <int R0>
-    BLUR_HD void store_item(const Ctx& c, int, int t, const float2 (&x)[R0]) const
+    BLUR_HD void store_item(const Ctx& c, int X, int t, const float2 (&x)[R0]) const
     {
         int jlo, jhi;
         ols_item_range(t, ax.halo, c.nvalid, jlo, jhi);
         const int x0 = c.s + t;
+        float* qc = c.qa + static_cast<size_t>(X) * nparts * srows * qpitch;
         if (nparts == 1) {
-            float* d = c.qa + x0;
+            float* d = qc + x0;
 #pragma unroll
-            for (int j = 0; j < R0; ++j)
-                if (j >= jlo && j <= jhi) {
-                    d[256 * j] = x[j].x;
-                    if (c.has_b) d[qpitch + 256 * j] = x[j].y;
-                }
+            for (int j = 0; j < R0; ++j) {
+                const bool va = j >= jlo && j <= jhi, vb = va && c.has_b;
+                if (va) d[256 * j] = x[j].x;
+                if (vb) d[qpitch + 256 * j] = x[j].y;
+            }
         } else {
 #pragma unroll
-            for (int j = 0; j < R0; ++j)
-                if (j >= jlo && j <= jhi) {
-                    const int xx = x0 + 256 * j;
-                    const int part = xx / cpart;
-                    float* d = c.qa + static_cast<size_t>(part) * srows * qpitch + (xx - part * cpart);
-                    d[0] = x[j].x;
-                    if (c.has_b) d[qpitch] = x[j].y;
-                }
+            for (int j = 0; j < R0; ++j) {
+                const bool va = j >= jlo && j <= jhi, vb = va && c.has_b;
+                const int xx = va ? x0 + 256 * j : 0;
+                const int part = xx / cpart;
+                float* d = qc + static_cast<size_t>(part) * srows * qpitch + (xx - part * cpart);
+                if (va) d[0] = x[j].x;
+                if (vb) d[qpitch] = x[j].y;
+            }
         }
     }
 };
 
 // ---- column pass IO: Q -> U ------------------------------------------------------------------
 // unit = (block * 3 + ch) * noct + oct.  One CTA transforms the four column pairs of a column
-// octet at once (kF = 4).  The block's L rows x 8 columns arrive in shared memory by TMA (kernel)
-// or a plain copy (emulator); rows outside the image are then patched with their reflect-101
+// octet at once (kF = 4).  Work item (X, t) owns tile rows 256 j + t of column pair X: it copies
+// them from Q (8 bytes each, cp.async in the kernel, plain loads in the emulator; rows outside Q
+// arrive as zeros), transforms them in pass A, and after the backward pass A refills the same
+// slots with the next unit's rows.  Rows outside the image are patched with their reflect-101
 // source (or zero) by ols_col_patch.
 struct OlsColIO {
     static constexpr bool kSmemInput = true;
     static constexpr int kF = 4;
+    const float* q;        // Q as received: [3][rows_total][qpitch]
+    int qpitch, rows_total;
     uint8_t* u;            // U base [3][noct][rows][8]
     int rows;              // image rows = line length
     int noct;              // column octets handled here
@@ -299,6 +341,7 @@ struct OlsColIO {
 
     struct Ctx {
         uint8_t* ua;       // U byte of (ch, oct, row 0, 0)
+        const float* qa;   // Q float of (ch, row 0, column 8*oct)
         int s;             // row of tile index 0 (may be negative)
         int nvalid;        // outputs this block keeps: tile indices [halo, halo + nvalid)
         int ch, oct;
@@ -312,18 +355,33 @@ struct OlsColIO {
         c.ch = rest % 3;
         const int b = rest / 3;
         c.ua = u + (static_cast<size_t>(c.ch) * noct + c.oct) * rows * 8;
+        c.qa = q + static_cast<size_t>(c.ch) * rows_total * qpitch + c.oct * 8;
         c.s = b * ax.V - ax.halo;
         c.nvalid = rows - b * ax.V < ax.V ? rows - b * ax.V : ax.V;
         c.interior = c.s >= 0 && c.s + ax.L <= rows;
         return c;
     }
-    BLUR_HD static uint32_t to_u8(float v)
+    // source of tile row i of column pair X, or nullptr if the row is outside Q
+    BLUR_HD const float* src(const Ctx& c, int X, int i) const
     {
-        // (uint8_t)(v + 0.5f): truncation, no clamp (Utils.hpp:189,204-206); negatives (undefined
-        // in the reference) saturate to 0
-        const float t = v + 0.5f;
-        return t > 0.f ? static_cast<uint32_t>(static_cast<int>(t)) & 255u : 0u;
+        const int r = c.s + i;
+        return (r >= 0 && r < rows_total) ? c.qa + static_cast<size_t>(r) * qpitch + 2 * X : nullptr;
     }
+    // (uint8_t)(v + 0.5f): truncation, no clamp (Utils.hpp:189,204-206); negatives (undefined
+    // in the reference) saturate to 0.  Returns the two bytes of a complex element packed.
+    BLUR_HD static uint32_t to_u8x2(float2 v)
+    {
+#ifdef __CUDA_ARCH__
+        const float2 t = __fadd2_rn(v, make_float2(0.5f, 0.5f));
+        return __byte_perm(__float2uint_rz(t.x), __float2uint_rz(t.y), 0x0040);   // cvt.rzi.u32 saturates < 0 to 0
+#else
+        const float a = v.x + 0.5f, b = v.y + 0.5f;
+        const uint32_t ua = a > 0.f ? static_cast<uint32_t>(static_cast<int>(a)) & 255u : 0u;
+        const uint32_t ub = b > 0.f ? static_cast<uint32_t>(static_cast<int>(b)) & 255u : 0u;
+        return ua | (ub << 8);
+#endif
+    }
+    BLUR_HD static uint32_t to_u8(float v) { return to_u8x2(make_float2(v, 0.f)) & 255u; }
     template <int R0>
     BLUR_HD void load_item(const Ctx&, int, int, float2 (&)[R0]) const {}
     template <int R0>
@@ -334,19 +392,19 @@ struct OlsColIO {
         uint16_t* d = reinterpret_cast<uint16_t*>(c.ua + (static_cast<ptrdiff_t>(c.s + t) * 8 + 2 * X));
 #pragma unroll
         for (int j = 0; j < R0; ++j)
-            if (j >= jlo && j <= jhi) d[1024 * j] = static_cast<uint16_t>(to_u8(x[j].x) | (to_u8(x[j].y) << 8));
+            if (j >= jlo && j <= jhi) d[1024 * j] = static_cast<uint16_t>(to_u8x2(x[j]));
     }
 };
 
-// Patch entry e = 4*i + X of an edge block (natural order in shared memory): rows outside the
-// image take their reflect-101 source, which is inside the same tile, or zero.
+// Patch entry e = 4*i + X of an edge block: rows outside the image take their reflect-101 source,
+// which is inside the same tile, or zero.  `s` = tile base (all four transforms).
 BLUR_HD void ols_col_patch(float2* __restrict__ s, int e, int s0, const OlsAxis& ax)
 {
     const int i = e >> 2, X = e & 3;
     const int g = s0 + i;
     if (g >= 0 && g < ax.len) return;
     const int src = ols_src(g, ax.len, ax.pad);
-    s[e] = src < 0 ? make_float2(0.f, 0.f) : s[4 * (src - s0) + X];
+    s[4 * ols_pad(i) + X] = src < 0 ? make_float2(0.f, 0.f) : s[4 * ols_pad(src - s0) + X];
 }
 
 }  // namespace blurb200

@@ -9,15 +9,15 @@ static cudaError_t launch_row(const OlsRowIO& io, const float2* twA, const float
                               cudaStream_t stream)
 {
     static bool configured = false;
-    constexpr int smem = ols_smem_bytes<R0, 1>();
+    constexpr int smem = ols_row_smem_bytes<R0>();
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(ols_row_kernel<R0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    const int grid = std::min(io.nunits, num_sms * ols_ctas_per_sm<R0, 1>());
+    const int grid = std::min(io.nunits, num_sms * ols_row_ctas_per_sm<R0>());
     if (grid <= 0) return cudaSuccess;
-    ols_row_kernel<R0><<<grid, kOlsThreads, smem, stream>>>(io, twA, twB, kt);
+    ols_row_kernel<R0><<<grid, ols_row_threads<R0>(), smem, stream>>>(io, twA, twB, kt);
     return cudaGetLastError();
 }
 
@@ -39,13 +39,13 @@ cudaError_t launch_ols_row(const OlsRowIO& io, const float2* twA, const float2* 
 int ols_resident_ctas(int R0)
 {
     switch (R0) {
-    case 4: return ols_ctas_per_sm<4, 1>();
-    case 6: return ols_ctas_per_sm<6, 1>();
-    case 8: return ols_ctas_per_sm<8, 1>();
-    case 12: return ols_ctas_per_sm<12, 1>();
-    case 16: return ols_ctas_per_sm<16, 1>();
-    case 24: return ols_ctas_per_sm<24, 1>();
-    case 32: return ols_ctas_per_sm<32, 1>();
+    case 4: return ols_row_ctas_per_sm<4>();
+    case 6: return ols_row_ctas_per_sm<6>();
+    case 8: return ols_row_ctas_per_sm<8>();
+    case 12: return ols_row_ctas_per_sm<12>();
+    case 16: return ols_row_ctas_per_sm<16>();
+    case 24: return ols_row_ctas_per_sm<24>();
+    case 32: return ols_row_ctas_per_sm<32>();
     default: return 0;
     }
 }

@@ -5,6 +5,7 @@
 // "thread" after another, with the kernel's barrier structure turned into sequential phases.
 // Lets the `-m "not gpu"` suite check the FFT decomposition, scrambled multiply, tile placement
 // and HBM layouts against the oracle without a GPU.
+#include <algorithm>
 #include <cstdio>
 #include <vector>
 #include "../../blur_algorithms_b200/csrc/fft_plan.hpp"
@@ -68,47 +69,57 @@ static void ols_row_units(const OlsRowIO& io, const OlsTables& T)
 {
 #pragma omp parallel
     {
-        std::vector<float2> smem(static_cast<size_t>(256) * R0);
+        std::vector<float2> smem(static_cast<size_t>(ols_tile_slots(R0)));
+        std::vector<uint8_t> raw(2 * ols_raw_pitch<R0>());
         float2* s = smem.data();
+        const uint8_t* lo = io.in;
+        const uint8_t* hi = io.in + static_cast<size_t>(io.rows) * io.cols * 3;
 #pragma omp for schedule(dynamic, 4)
         for (int unit = 0; unit < io.nunits; ++unit) {
-            const OlsRowIO::Ctx ctx = io.begin(unit);
-            for (int t = 0; t < 256; ++t) ols_pass_a_fwd<R0, 1>(s, s, 0, t, T.twA.data(), io, ctx);
-            for (int it = 0; it < 16 * R0; ++it) ols_pass_b<false, 1>(s, it, T.twB.data());
-            for (int it = 0; it < 16 * R0; ++it) ols_mid<R0, 1>(s, it, T.kt.data());
-            for (int it = 0; it < 16 * R0; ++it) ols_pass_b<true, 1>(s, it, T.twB.data());
-            for (int t = 0; t < 256; ++t) ols_pass_a_inv<R0, 1>(s, 0, t, T.twA.data(), io, ctx);
+            const OlsRowIO::Ctx ctx = io.begin(unit, raw.data(), ols_raw_pitch<R0>());
+            // what ols_row_stage's 16-byte copies deliver
+            std::fill(raw.begin(), raw.end(), 0xCD);
+            for (int k = 0; k < 2 && ctx.ra + k < io.rows; ++k) {
+                const OlsRowIO::Stage st = io.stage_of(ctx.ra + k, ctx.s, ctx.w0, ctx.w1);
+                for (int e = 0; e < 16 * st.nvec; ++e)
+                    if (st.src + e >= lo && st.src + e < hi) raw[k * ols_raw_pitch<R0>() + st.dst + e] = st.src[e];
+            }
+            if (!ctx.interior)
+                for (int e = 0; e < 2 * 256 * R0; ++e) io.fixup(ctx, e);
+            for (int ch = 0; ch < 3; ++ch) {
+                for (int t = 0; t < 256; ++t) ols_pass_a_fwd<R0, 1>(s, ch, t, T.twA.data(), io, ctx);
+                for (int it = 0; it < 16 * R0; ++it) ols_pass_b<false, 1>(s, it, T.twB.data());
+                for (int it = 0; it < 16 * R0; ++it) ols_mid<R0, 1>(s, it, T.kt.data());
+                for (int it = 0; it < 16 * R0; ++it) ols_pass_b<true, 1>(s, it, T.twB.data());
+                for (int t = 0; t < 256; ++t) ols_pass_a_inv<R0, 1>(s, ch, t, T.twA.data(), io, ctx);
+            }
         }
     }
 }
 
 // q = Q as received: [3][rows_total][qpitch]
 template <int R0>
-static void ols_col_units(const OlsColIO& io, const float* q, int qpitch, int rows_total, const OlsTables& T)
+static void ols_col_units(const OlsColIO& io, const OlsTables& T)
 {
     constexpr int F = 4, L = 256 * R0;
 #pragma omp parallel
     {
-        std::vector<float2> smem(static_cast<size_t>(F) * L), nat(static_cast<size_t>(F) * L);
+        std::vector<float2> smem(static_cast<size_t>(F) * ols_tile_slots(R0));
 #pragma omp for schedule(dynamic, 4)
         for (int unit = 0; unit < io.nunits; ++unit) {
             const OlsColIO::Ctx ctx = io.begin(unit);
-            // what the TMA boxes deliver: rows outside the tensor are zero-filled
+            // what ols_col_fetch's copies deliver: rows outside Q are zero-filled
+            std::fill(smem.begin(), smem.end(), make_float2(-777.f, 777.f));
             for (int i = 0; i < L; ++i)
                 for (int X = 0; X < F; ++X) {
-                    const int r = ctx.s + i;
-                    float2 v = make_float2(0.f, 0.f);
-                    if (r >= 0 && r < rows_total) {
-                        const float* p = q + (static_cast<size_t>(ctx.ch) * rows_total + r) * qpitch + ctx.oct * 8 + 2 * X;
-                        v = make_float2(p[0], p[1]);
-                    }
-                    nat[static_cast<size_t>(F) * i + X] = v;
+                    const float* p = io.src(ctx, X, i);
+                    smem[static_cast<size_t>(F) * ols_pad(i) + X] = p ? make_float2(p[0], p[1]) : make_float2(0.f, 0.f);
                 }
             if (!ctx.interior)
-                for (int e = 0; e < F * L; ++e) ols_col_patch(nat.data(), e, ctx.s, io.ax);
+                for (int e = 0; e < F * L; ++e) ols_col_patch(smem.data(), e, ctx.s, io.ax);
             for (int X = 0; X < F; ++X) {
                 float2* sx = smem.data() + X;
-                for (int t = 0; t < 256; ++t) ols_pass_a_fwd<R0, F>(sx, nat.data() + X, X, t, T.twA.data(), io, ctx);
+                for (int t = 0; t < 256; ++t) ols_pass_a_fwd<R0, F>(sx, X, t, T.twA.data(), io, ctx);
                 for (int it = 0; it < 16 * R0; ++it) ols_pass_b<false, F>(sx, it, T.twB.data());
                 for (int it = 0; it < 16 * R0; ++it) ols_mid<R0, F>(sx, it, T.kt.data());
                 for (int it = 0; it < 16 * R0; ++it) ols_pass_b<true, F>(sx, it, T.twB.data());
@@ -125,7 +136,7 @@ static int ols_row_pass(const uint8_t* in_stripe, float* q, const GaussGeometry&
     OlsRowIO io{};
     io.in = in_stripe; io.q = q; io.rows = sg.valid_rows; io.cols = gg.cols; io.npairs = (sg.valid_rows + 1) / 2;
     io.srows = sg.stripe_rows; io.qpitch = sg.qpitch; io.cpart = sg.cpart; io.nparts = nranks;
-    io.ax = sg.ols_row; io.nunits = io.ax.nblocks * 3 * io.npairs;
+    io.ax = sg.ols_row; io.nunits = io.ax.nblocks * io.npairs;
     const OlsTables T(io.ax.R0, sigma, gg.ksize);
 #define F_(R) ols_row_units<R>(io, T)
     OLS_R0_SWITCH(io.ax.R0, F_)
@@ -144,7 +155,8 @@ static int ols_col_pass(const float* q_recv, uint8_t* out_cols, const GaussGeome
     std::vector<uint8_t> U(static_cast<size_t>(3) * io.noct * rows * 8);
     io.u = U.data(); io.rows = rows; io.ax = sg.ols_col; io.nunits = io.ax.nblocks * 3 * io.noct;
     const OlsTables T(io.ax.R0, sigma, gg.ksize);
-#define F_(R) ols_col_units<R>(io, q_recv, sg.qpitch, nranks * sg.stripe_rows, T)
+    io.q = q_recv; io.qpitch = sg.qpitch; io.rows_total = nranks * sg.stripe_rows;
+#define F_(R) ols_col_units<R>(io, T)
     OLS_R0_SWITCH(io.ax.R0, F_)
 #undef F_
     for (int r = 0; r < rows; ++r)
