@@ -2,7 +2,7 @@
 """Generates dft_codelets2.cuh: straight-line small DFTs on packed complex values.
 
 Each codelet `cdftR_f` / `cdftR_b` (forward e^{-i..} / backward e^{+i..}, unscaled) transforms R
-complex values held as float2 x[R] in place, natural order in and out, using only the packed
+complex values held as cplx x[R] (cplx2.cuh) in place, natural order in and out, using only the packed
 complex primitives of cplx2.cuh (one FADD2 / FMUL2 / FFMA2 each).  They are the per-thread
 butterflies of the overlap-save FFT passes in ols_core.cuh.
 
@@ -43,7 +43,7 @@ class Gen:
     def e(self, expr: str) -> str:
         self.n += 1
         v = f"t{self.n}"
-        self.lines.append(f"    const float2 {v} = {expr};")
+        self.lines.append(f"    const cplx {v} = {expr};")
         self.ops += 1
         return v
 
@@ -101,7 +101,7 @@ class Gen:
             return a
         if r == 2:
             return self.e(f"cscale({a}, -1.0f)")
-        zero = "make_float2(0.f, 0.f)"
+        zero = "czero()"
         return self.e(f"{'caddi' if r == 1 else 'csubi'}({zero}, {a})")
 
     # ---- base DFTs
@@ -196,7 +196,7 @@ def codelet(R: int, sign: int) -> str:
     xin = []
     for j in range(R):
         g.n += 1
-        g.lines.append(f"    const float2 t{g.n} = x[{j}];")
+        g.lines.append(f"    const cplx t{g.n} = x[{j}];")
         xin.append((f"t{g.n}", 0))
     y = g.dft(xin)
     outs = [g.materialise(v) for v in y]
@@ -204,7 +204,7 @@ def codelet(R: int, sign: int) -> str:
     body = "\n".join(g.lines)
     wb = "\n".join(f"    x[{k}] = {outs[k]};" for k in range(R))
     return (f"// radix {R} {'forward' if sign < 0 else 'backward'}: {g.ops} packed instructions\n"
-            f"BLUR_HD void {name}(float2* __restrict__ x)\n{{\n{body}\n{wb}\n}}\n")
+            f"BLUR_HD void {name}(cplx* __restrict__ x)\n{{\n{body}\n{wb}\n}}\n")
 
 
 def main() -> None:
@@ -215,10 +215,10 @@ def main() -> None:
         out.append(codelet(R, -1))
         out.append(codelet(R, +1))
     out.append("template <int R, bool INV> struct CDft;\n")
-    out.append("template <bool INV> struct CDft<1, INV> { static BLUR_HD void run(float2*) {} };")
+    out.append("template <bool INV> struct CDft<1, INV> { static BLUR_HD void run(cplx*) {} };")
     for R in RADICES:
-        out.append(f"template <> struct CDft<{R}, false> {{ static BLUR_HD void run(float2* x) {{ cdft{R}_f(x); }} }};")
-        out.append(f"template <> struct CDft<{R}, true>  {{ static BLUR_HD void run(float2* x) {{ cdft{R}_b(x); }} }};")
+        out.append(f"template <> struct CDft<{R}, false> {{ static BLUR_HD void run(cplx* x) {{ cdft{R}_f(x); }} }};")
+        out.append(f"template <> struct CDft<{R}, true>  {{ static BLUR_HD void run(cplx* x) {{ cdft{R}_b(x); }} }};")
     out.append("\n}  // namespace blurb200\n")
     sys.stdout.write("\n".join(out))
 

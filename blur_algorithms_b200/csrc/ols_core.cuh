@@ -82,8 +82,8 @@ BLUR_HD void ols_item_range(int t, int halo, int nvalid, int& jlo, int& jhi)
 //   static constexpr bool kSmemInput      block already sits in shared memory in natural order
 //   static constexpr int  kF              transforms interleaved per CTA
 //   Ctx   begin(int unit) const
-//   void load_item <R0>(const Ctx&, int X, int t, float2 (&x)[R0]) const    x[j] = tile_X[256 j + t]
-//   void store_item<R0>(const Ctx&, int X, int t, const float2 (&x)[R0]) const
+//   void load_item <R0>(const Ctx&, int X, int t, cplx (&x)[R0]) const    x[j] = tile_X[256 j + t]
+//   void store_item<R0>(const Ctx&, int X, int t, const cplx (&x)[R0]) const
 // The valid outputs of a block are tile indices [halo, halo + nvalid); item t owns j in
 // [jlo, jhi] of them (ols_item_range), so the per-element test is a compare of two registers
 // with an immediate.
@@ -91,11 +91,11 @@ BLUR_HD void ols_item_range(int t, int halo, int nvalid, int& jlo, int& jhi)
 
 // ---- pass A, forward: item (X, t), t in [0, 256)
 template <int R0, int F, class IO>
-BLUR_HD void ols_pass_a_fwd(float2* sx, int X, int t, const float2* __restrict__ twA, const IO& io,
+BLUR_HD void ols_pass_a_fwd(cplx* sx, int X, int t, const cplx* __restrict__ twA, const IO& io,
                             const typename IO::Ctx& ctx)
 {
-    float2 x[R0];
-    float2* base = sx + F * ols_pad(t);
+    cplx x[R0];
+    cplx* base = sx + F * ols_pad(t);
     if (IO::kSmemInput) {
 #pragma unroll
         for (int j = 0; j < R0; ++j) x[j] = base[F * 272 * j];
@@ -103,18 +103,18 @@ BLUR_HD void ols_pass_a_fwd(float2* sx, int X, int t, const float2* __restrict__
         io.template load_item<R0>(ctx, X, t, x);
     }
     CDft<R0, false>::run(x);
-    cstore(base, x[0]);
+    *(base) = x[0];
 #pragma unroll
-    for (int q = 1; q < R0; ++q) cstore(base + F * 272 * q, cmul(x[q], twA[(q - 1) * 256 + t]));
+    for (int q = 1; q < R0; ++q) base[F * 272 * q] = cmul(x[q], twA[(q - 1) * 256 + t]);
 }
 
 // ---- pass A, backward
 template <int R0, int F, class IO>
-BLUR_HD void ols_pass_a_inv(const float2* __restrict__ sx, int X, int t, const float2* __restrict__ twA, const IO& io,
+BLUR_HD void ols_pass_a_inv(const cplx* __restrict__ sx, int X, int t, const cplx* __restrict__ twA, const IO& io,
                             const typename IO::Ctx& ctx)
 {
-    float2 x[R0];
-    const float2* base = sx + F * ols_pad(t);
+    cplx x[R0];
+    const cplx* base = sx + F * ols_pad(t);
     x[0] = base[0];
 #pragma unroll
     for (int q = 1; q < R0; ++q) x[q] = cmulc(base[F * 272 * q], twA[(q - 1) * 256 + t]);
@@ -124,35 +124,35 @@ BLUR_HD void ols_pass_a_inv(const float2* __restrict__ sx, int X, int t, const f
 
 // ---- pass B: item (X, it), it in [0, 16*R0): k0 = it >> 4, t = it & 15
 template <bool INV, int F>
-BLUR_HD void ols_pass_b(float2* __restrict__ sx, int it, const float2* __restrict__ twB)
+BLUR_HD void ols_pass_b(cplx* __restrict__ sx, int it, const cplx* __restrict__ twB)
 {
     const int t = it & 15;
-    float2* blk = sx + F * (272 * (it >> 4) + t);
-    float2 x[16];
+    cplx* blk = sx + F * (272 * (it >> 4) + t);
+    cplx x[16];
     if (!INV) {
 #pragma unroll
         for (int j = 0; j < 16; ++j) x[j] = blk[F * 17 * j];
         CDft<16, false>::run(x);
-        cstore(blk, x[0]);
+        *(blk) = x[0];
 #pragma unroll
-        for (int q = 1; q < 16; ++q) cstore(blk + F * 17 * q, cmul(x[q], twB[(q - 1) * 16 + t]));
+        for (int q = 1; q < 16; ++q) blk[F * 17 * q] = cmul(x[q], twB[(q - 1) * 16 + t]);
     } else {
         x[0] = blk[0];
 #pragma unroll
         for (int q = 1; q < 16; ++q) x[q] = cmulc(blk[F * 17 * q], twB[(q - 1) * 16 + t]);
         CDft<16, true>::run(x);
 #pragma unroll
-        for (int j = 0; j < 16; ++j) cstore(blk + F * 17 * j, x[j]);
+        for (int j = 0; j < 16; ++j) *(blk + F * 17 * j) = x[j];
     }
 }
 
 // ---- mid: item (X, u), u in [0, 16*R0).  kt[q * (16*R0) + u] = Re K[k0 + R0*(k1 + 16 q)] / L
 // with u = 16*k0 + k1.
 template <int R0, int F>
-BLUR_HD void ols_mid(float2* __restrict__ sx, int u, const float* __restrict__ kt)
+BLUR_HD void ols_mid(cplx* __restrict__ sx, int u, const float* __restrict__ kt)
 {
-    float2* grp = sx + F * 17 * u;
-    float2 x[16];
+    cplx* grp = sx + F * 17 * u;
+    cplx x[16];
 #pragma unroll
     for (int j = 0; j < 16; ++j) x[j] = grp[F * j];
     CDft<16, false>::run(x);
@@ -160,7 +160,7 @@ BLUR_HD void ols_mid(float2* __restrict__ sx, int u, const float* __restrict__ k
     for (int q = 0; q < 16; ++q) x[q] = cscale(x[q], kt[q * (16 * R0) + u]);
     CDft<16, true>::run(x);
 #pragma unroll
-    for (int j = 0; j < 16; ++j) cstore(grp + F * j, x[j]);
+    for (int j = 0; j < 16; ++j) *(grp + F * j) = x[j];
 }
 
 // ---- row pass IO: uint8 interleaved BGR lines -> Q -------------------------------------------
@@ -280,20 +280,20 @@ struct OlsRowIO {
     }
     // X = channel
     template <int R0>
-    BLUR_HD void load_item(const Ctx& c, int X, int t, float2 (&x)[R0]) const
+    BLUR_HD void load_item(const Ctx& c, int X, int t, cplx (&x)[R0]) const
     {
         const uint8_t* pa = c.raw + c.ia + 3 * t + X;
         const int db = c.ib - c.ia;
         if (c.has_b) {
 #pragma unroll
-            for (int j = 0; j < R0; ++j) x[j] = make_float2(u8f(pa[768 * j]), u8f(pa[db + 768 * j]));
+            for (int j = 0; j < R0; ++j) x[j] = cpack(u8f(pa[768 * j]), u8f(pa[db + 768 * j]));
         } else {
 #pragma unroll
-            for (int j = 0; j < R0; ++j) x[j] = make_float2(u8f(pa[768 * j]), 0.f);
+            for (int j = 0; j < R0; ++j) x[j] = cpack(u8f(pa[768 * j]), 0.f);
         }
     }
     template <int R0>
-    BLUR_HD void store_item(const Ctx& c, int X, int t, const float2 (&x)[R0]) const
+    BLUR_HD void store_item(const Ctx& c, int X, int t, const cplx (&x)[R0]) const
     {
         int jlo, jhi;
         ols_item_range(t, ax.halo, c.nvalid, jlo, jhi);
@@ -304,8 +304,8 @@ struct OlsRowIO {
 #pragma unroll
             for (int j = 0; j < R0; ++j) {
                 const bool va = j >= jlo && j <= jhi, vb = va && c.has_b;
-                if (va) d[256 * j] = x[j].x;
-                if (vb) d[qpitch + 256 * j] = x[j].y;
+                if (va) d[256 * j] = cre(x[j]);
+                if (vb) d[qpitch + 256 * j] = cim(x[j]);
             }
         } else {
 #pragma unroll
@@ -314,8 +314,8 @@ struct OlsRowIO {
                 const int xx = va ? x0 + 256 * j : 0;
                 const int part = xx / cpart;
                 float* d = qc + static_cast<size_t>(part) * srows * qpitch + (xx - part * cpart);
-                if (va) d[0] = x[j].x;
-                if (vb) d[qpitch] = x[j].y;
+                if (va) d[0] = cre(x[j]);
+                if (vb) d[qpitch] = cim(x[j]);
             }
         }
     }
@@ -369,23 +369,23 @@ struct OlsColIO {
     }
     // (uint8_t)(v + 0.5f): truncation, no clamp (Utils.hpp:189,204-206); negatives (undefined
     // in the reference) saturate to 0.  Returns the two bytes of a complex element packed.
-    BLUR_HD static uint32_t to_u8x2(float2 v)
+    BLUR_HD static uint32_t to_u8x2(cplx v)
     {
 #ifdef __CUDA_ARCH__
-        const float2 t = __fadd2_rn(v, make_float2(0.5f, 0.5f));
-        return __byte_perm(__float2uint_rz(t.x), __float2uint_rz(t.y), 0x0040);   // cvt.rzi.u32 saturates < 0 to 0
+        const cplx t = cadd(v, cpack(0.5f, 0.5f));
+        return __byte_perm(__float2uint_rz(cre(t)), __float2uint_rz(cim(t)), 0x0040);   // cvt.rzi.u32 saturates < 0 to 0
 #else
-        const float a = v.x + 0.5f, b = v.y + 0.5f;
+        const float a = cre(v) + 0.5f, b = cim(v) + 0.5f;
         const uint32_t ua = a > 0.f ? static_cast<uint32_t>(static_cast<int>(a)) & 255u : 0u;
         const uint32_t ub = b > 0.f ? static_cast<uint32_t>(static_cast<int>(b)) & 255u : 0u;
         return ua | (ub << 8);
 #endif
     }
-    BLUR_HD static uint32_t to_u8(float v) { return to_u8x2(make_float2(v, 0.f)) & 255u; }
+    BLUR_HD static uint32_t to_u8(float v) { return to_u8x2(cpack(v, 0.f)) & 255u; }
     template <int R0>
-    BLUR_HD void load_item(const Ctx&, int, int, float2 (&)[R0]) const {}
+    BLUR_HD void load_item(const Ctx&, int, int, cplx (&)[R0]) const {}
     template <int R0>
-    BLUR_HD void store_item(const Ctx& c, int X, int t, const float2 (&x)[R0]) const
+    BLUR_HD void store_item(const Ctx& c, int X, int t, const cplx (&x)[R0]) const
     {
         int jlo, jhi;
         ols_item_range(t, ax.halo, c.nvalid, jlo, jhi);
@@ -398,13 +398,13 @@ struct OlsColIO {
 
 // Patch entry e = 4*i + X of an edge block: rows outside the image take their reflect-101 source,
 // which is inside the same tile, or zero.  `s` = tile base (all four transforms).
-BLUR_HD void ols_col_patch(float2* __restrict__ s, int e, int s0, const OlsAxis& ax)
+BLUR_HD void ols_col_patch(cplx* __restrict__ s, int e, int s0, const OlsAxis& ax)
 {
     const int i = e >> 2, X = e & 3;
     const int g = s0 + i;
     if (g >= 0 && g < ax.len) return;
     const int src = ols_src(g, ax.len, ax.pad);
-    s[4 * ols_pad(i) + X] = src < 0 ? make_float2(0.f, 0.f) : s[4 * ols_pad(src - s0) + X];
+    s[4 * ols_pad(i) + X] = src < 0 ? czero() : s[4 * ols_pad(src - s0) + X];
 }
 
 }  // namespace blurb200

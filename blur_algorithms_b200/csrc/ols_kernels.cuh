@@ -85,10 +85,13 @@ __device__ __forceinline__ void ols_row_stage(const OlsRowIO& io, int unit, uint
 
 template <int R0>
 __global__ void __launch_bounds__(ols_row_threads<R0>(), ols_row_ctas_per_sm<R0>())
-ols_row_kernel(const __grid_constant__ OlsRowIO io, const float2* __restrict__ twA, const float2* __restrict__ twB,
+ols_row_kernel(const __grid_constant__ OlsRowIO io, const float2* __restrict__ twA_, const float2* __restrict__ twB_,
                const float* __restrict__ kt)
 {
-    extern __shared__ __align__(128) float2 smem[];
+    extern __shared__ __align__(128) float2 smem_f2[];
+    cplx* smem = reinterpret_cast<cplx*>(smem_f2);
+    const cplx* twA = reinterpret_cast<const cplx*>(twA_);
+    const cplx* twB = reinterpret_cast<const cplx*>(twB_);
     constexpr int NT = ols_row_threads<R0>();
     constexpr int NB = 16 * R0;
     uint8_t* raw = reinterpret_cast<uint8_t*>(smem + 272 * R0);
@@ -146,10 +149,10 @@ __device__ __forceinline__ void cp_async16_zfill(void* dst, const void* src, boo
 // Lanes with even X fetch, for themselves and their odd neighbour, the R0 tile rows item t owns
 // for `ctx`: 16 bytes = column pairs (X, X+1) of one Q row, straight into the two adjacent slots.
 template <int R0>
-__device__ __forceinline__ void ols_col_fetch(const OlsColIO& io, const OlsColIO::Ctx& ctx, float2* sx, int X, int t)
+__device__ __forceinline__ void ols_col_fetch(const OlsColIO& io, const OlsColIO::Ctx& ctx, cplx* sx, int X, int t)
 {
     if (X & 1) return;
-    float2* base = sx + 4 * ols_pad(t);
+    cplx* base = sx + 4 * ols_pad(t);
     const int r0 = ctx.s + t;
     const float* p = ctx.qa + static_cast<ptrdiff_t>(r0) * io.qpitch + 2 * X;
     const size_t step = static_cast<size_t>(256) * io.qpitch;
@@ -168,15 +171,18 @@ __device__ __forceinline__ void ols_col_fetch(const OlsColIO& io, const OlsColIO
 
 template <int R0>
 __global__ void __launch_bounds__(4 * kOlsThreads, ols_ctas_per_sm<R0, 4>())
-ols_col_kernel(const __grid_constant__ OlsColIO io, const float2* __restrict__ twA, const float2* __restrict__ twB,
+ols_col_kernel(const __grid_constant__ OlsColIO io, const float2* __restrict__ twA_, const float2* __restrict__ twB_,
                const float* __restrict__ kt)
 {
-    extern __shared__ __align__(128) float2 smem[];
+    extern __shared__ __align__(128) float2 smem_f2[];
+    cplx* smem = reinterpret_cast<cplx*>(smem_f2);
+    const cplx* twA = reinterpret_cast<const cplx*>(twA_);
+    const cplx* twB = reinterpret_cast<const cplx*>(twB_);
     constexpr int F = 4, NT = F * kOlsThreads;
     constexpr int L = 256 * R0;
     const int tid = threadIdx.x;
     const int X = tid & (F - 1), sub = tid >> 2;          // work item = (transform X, index)
-    float2* sx = smem + X;
+    cplx* sx = smem + X;
     constexpr int NB = 16 * R0;
     int unit = blockIdx.x;
     if (unit < io.nunits) {

@@ -113,7 +113,7 @@ static void ols_col_units(const OlsColIO& io, const OlsTables& T)
             for (int i = 0; i < L; ++i)
                 for (int X = 0; X < F; ++X) {
                     const float* p = io.src(ctx, X, i);
-                    smem[static_cast<size_t>(F) * ols_pad(i) + X] = p ? make_float2(p[0], p[1]) : make_float2(0.f, 0.f);
+                    smem[static_cast<size_t>(F) * ols_pad(i) + X] = p ? cpack(p[0], p[1]) : czero();
                 }
             if (!ctx.interior)
                 for (int e = 0; e < F * L; ++e) ols_col_patch(smem.data(), e, ctx.s, io.ax);
