@@ -217,6 +217,8 @@ def main() -> None:
         h_img = torch.from_numpy(stripe_np).pin_memory()
         d_in = h_img.to(dev)
         plan = sb.plan
+        config["exchange"] = ("fused: row-pass epilogue stores into the owners' symmetric-memory buffers over NVLink"
+                              if sb.fused else "NCCL all_to_all of the float32 intermediate")
         step = lambda: sb.run(d_in)                      # noqa: E731
 
     # ---- device-resident timing
@@ -266,11 +268,13 @@ def main() -> None:
         del q, oc
     else:
         g = sb.geom
-        sb.plan.row_pass(d_in, sb.q_send); sb.plan.col_pass(sb.q_recv, sb.out_cols)
-        torch.cuda.synchronize()
+        rp = (lambda: sb.plan.row_pass_peer(d_in, sb.peer_ptrs)) if sb.fused else (lambda: sb.plan.row_pass(d_in, sb.q_send))
+        barrier()
+        rp(); sb.plan.col_pass(sb.q_recv, sb.out_cols)
+        barrier()
         e[0].record(stream)
         for _ in range(reps):
-            sb.plan.row_pass(d_in, sb.q_send)
+            rp()
         e[1].record(stream)
         for _ in range(reps):
             sb.plan.col_pass(sb.q_recv, sb.out_cols)
@@ -279,7 +283,9 @@ def main() -> None:
         row_ms = e[0].elapsed_time(e[1]) / reps
         colil_ms = e[1].elapsed_time(e[2]) / reps
         pass_px = g.valid_rows * cols
-    dom_name, dom_ms = ("fft_conv_kernel<RowIO>", row_ms) if row_ms >= colil_ms else ("fft_conv_kernel<ColIO> (+interleave_u8_kernel)", colil_ms)
+    algo = plan.info["algo"]
+    kn = ("ols_row_kernel", "ols_col_kernel (+interleave_oct_kernel)") if algo == 1 else ("fft_conv_kernel<RowIO>", "fft_conv_kernel<ColIO> (+interleave_u8_kernel)")
+    dom_name, dom_ms = (kn[0], row_ms) if row_ms >= colil_ms else (kn[1], colil_ms)
     achieved = ALG_BYTES_PER_PX_PASS * pass_px / (dom_ms * 1e-3) / 1e9
     traffic = None
     tp = os.path.join(ROOT, "profiles", "traffic.json")
@@ -337,7 +343,7 @@ def main() -> None:
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
                 "dtype": "f32", "data": "synthetic", "config": config, "roofline": roofline, "clocks": clocks,
                 "e2e": e2e, "gpu_launches": int(launches), "impl": "b200",
-                "plan": {k: plan.info[k] for k in ("n_row", "n_col", "threads_row", "threads_col", "batch_row", "batch_col", "smem_row", "smem_col")}}
+                "plan": {k: plan.info[k] for k in ("algo", "n_row", "n_col", "ols_L_row", "ols_L_col", "ols_V_row", "ols_V_col", "ols_nblocks_row", "ols_nblocks_col")}}
         if cpu is not None:
             line["cpu_baseline"] = cpu
         print(json.dumps(line))

@@ -158,6 +158,12 @@ class GaussPlan:
     def row_pass(self, d_in_stripe, d_q, stream: int | None = None):
         check(lib.blur_b200_gauss_row_pass(self._h, _ptr(d_in_stripe), _ptr(d_q), _stream() if stream is None else stream))
 
+    def row_pass_peer(self, d_in_stripe, q_peer_ptrs, stream: int | None = None):
+        """Row pass whose epilogue stores into the peers' receive buffers (fused exchange)."""
+        arr = (C.c_void_p * len(q_peer_ptrs))(*[int(p) for p in q_peer_ptrs])
+        check(lib.blur_b200_gauss_row_pass_peer(self._h, _ptr(d_in_stripe), arr, len(q_peer_ptrs),
+                                                _stream() if stream is None else stream))
+
     def col_pass(self, d_q_chunks, d_out_cols, stream: int | None = None):
         check(lib.blur_b200_gauss_col_pass(self._h, _ptr(d_q_chunks), _ptr(d_out_cols), _stream() if stream is None else stream))
 

@@ -492,7 +492,7 @@ int plan_create(blur_b200_plan** out, int rows, int cols, double sigma, int mode
     return BLUR_B200_OK;
 }
 
-int run_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, float* d_q, cudaStream_t st)
+int run_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, float* d_q, cudaStream_t st, float* const* peers = nullptr)
 {
     if (p->valid_rows <= 0) return BLUR_B200_OK;
     if (p->algo == 1) {
@@ -503,6 +503,10 @@ int run_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, float* d_q, cuda
         io.srows = p->stripe_rows; io.qpitch = p->qpitch; io.cpart = p->cpart; io.nparts = p->nranks;
         io.ax = p->ols_row;
         io.nunits = io.ax.nblocks * io.npairs;
+        if (peers && p->nranks > 1) {
+            io.peer = 1; io.rank = p->rank;
+            for (int k = 0; k < p->nranks; ++k) io.qpeer[k] = peers[k];
+        }
         CU_TRY(launch_ols_row(io, p->d_ols_twa_row, p->d_ols_twb, p->d_ols_kt_row, p->num_sms, st));
         ++g_launches;
         return BLUR_B200_OK;
@@ -708,6 +712,15 @@ int blur_b200_gauss_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, floa
 {
     if (!p || !d_in_stripe || !d_q) return BLUR_B200_EINVAL;
     return run_row_pass(p, d_in_stripe, d_q, static_cast<cudaStream_t>(stream));
+}
+
+int blur_b200_gauss_row_pass_peer(blur_b200_plan* p, const uint8_t* d_in_stripe, float* const* q_peers, int npeers, void* stream)
+{
+    if (!p || !d_in_stripe || !q_peers || npeers != p->nranks || npeers > OlsRowIO::kMaxPeers) return BLUR_B200_EINVAL;
+    if (p->algo != 1) return BLUR_B200_ESIZE;      // only the overlap-save row kernel has the fused epilogue
+    for (int k = 0; k < npeers; ++k)
+        if (!q_peers[k]) return BLUR_B200_EINVAL;
+    return run_row_pass(p, d_in_stripe, p->d_q, static_cast<cudaStream_t>(stream), q_peers);
 }
 
 int blur_b200_gauss_col_pass(blur_b200_plan* p, const float* d_q_chunks, uint8_t* d_out_cols, void* stream)

@@ -108,16 +108,27 @@ BLUR_HD void ols_pass_a_fwd(cplx* sx, int X, int t, const cplx* __restrict__ twA
     for (int q = 1; q < R0; ++q) base[F * 272 * q] = cmul(x[q], twA[(q - 1) * 256 + t]);
 }
 
-// ---- pass A, backward
+// ---- pass A, backward.  The conjugate twiddles are the first thing an item needs, and the table
+// (22 KB at R0 = 12) does not stay in the few KB of L1 left beside the tiles, so each item
+// consumes twiddles fetched one item ahead: `w` holds those of item t on entry and those of item
+// t_next on exit (t_next >= 256: none).  The first item's are loaded before the barrier.
+template <int R0>
+BLUR_HD void ols_tw_load(cplx (&w)[R0], const cplx* __restrict__ twA, int t)
+{
+#pragma unroll
+    for (int q = 1; q < R0; ++q) w[q] = twA[(q - 1) * 256 + t];
+}
+
 template <int R0, int F, class IO>
-BLUR_HD void ols_pass_a_inv(const cplx* __restrict__ sx, int X, int t, const cplx* __restrict__ twA, const IO& io,
-                            const typename IO::Ctx& ctx)
+BLUR_HD void ols_pass_a_inv(const cplx* __restrict__ sx, int X, int t, int t_next, const cplx* __restrict__ twA,
+                            cplx (&w)[R0], const IO& io, const typename IO::Ctx& ctx)
 {
     cplx x[R0];
     const cplx* base = sx + F * ols_pad(t);
     x[0] = base[0];
 #pragma unroll
-    for (int q = 1; q < R0; ++q) x[q] = cmulc(base[F * 272 * q], twA[(q - 1) * 256 + t]);
+    for (int q = 1; q < R0; ++q) x[q] = cmulc(base[F * 272 * q], w[q]);
+    if (t_next < 256) ols_tw_load<R0>(w, twA, t_next);
     CDft<R0, true>::run(x);
     io.template store_item<R0>(ctx, X, t, x);
 }
@@ -210,6 +221,13 @@ struct OlsRowIO {
     int nparts;
     int nunits;            // nblocks * npairs
     OlsAxis ax;            // len = cols
+    // Fused exchange (nparts > 1, peer != 0): the epilogue stores each output straight into the
+    // Q buffer of the GPU that owns its column, qpeer[part], over NVLink peer mappings, as block
+    // `rank` of that buffer ([3][nparts][srows][qpitch], block index = source rank): the
+    // distributed flip_block (Source.cpp:540) costs no pass over HBM and no collective call.
+    static constexpr int kMaxPeers = 8;
+    float* qpeer[kMaxPeers];
+    int rank, peer;
 
     struct Stage {
         const uint8_t* src;  // 16-byte aligned global address of the first vector
@@ -313,7 +331,8 @@ struct OlsRowIO {
                 const bool va = j >= jlo && j <= jhi, vb = va && c.has_b;
                 const int xx = va ? x0 + 256 * j : 0;
                 const int part = xx / cpart;
-                float* d = qc + static_cast<size_t>(part) * srows * qpitch + (xx - part * cpart);
+                float* d = peer ? qpeer[part] + (static_cast<size_t>(X * nparts + rank) * srows + c.ra) * qpitch + (xx - part * cpart)
+                                : qc + static_cast<size_t>(part) * srows * qpitch + (xx - part * cpart);
                 if (va) d[0] = cre(x[j]);
                 if (vb) d[qpitch] = cim(x[j]);
             }

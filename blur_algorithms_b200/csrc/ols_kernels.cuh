@@ -130,9 +130,11 @@ ols_row_kernel(const __grid_constant__ OlsRowIO io, const float2* __restrict__ t
             __syncwarp();
 #pragma unroll 1
             for (int it = tid; it < NB; it += NT) ols_pass_b<true, 1>(smem, it, twB);
+            cplx w[R0];
+            if (tid < 256) ols_tw_load<R0>(w, twA, tid);
             __syncthreads();
 #pragma unroll 1
-            for (int t = tid; t < 256; t += NT) ols_pass_a_inv<R0, 1>(smem, ch, t, twA, io, ctx);
+            for (int t = tid; t < 256; t += NT) ols_pass_a_inv<R0, 1>(smem, ch, t, t + NT, twA, w, io, ctx);
             // no barrier: the next pass A (forward) item t is this same thread on the same slots
         }
     }
@@ -212,17 +214,19 @@ ols_col_kernel(const __grid_constant__ OlsColIO io, const float2* __restrict__ t
         __syncthreads();
 #pragma unroll 1
         for (int it = sub; it < NB; it += kOlsThreads) ols_pass_b<true, F>(sx, it, twB);
+        cplx w[R0];
+        ols_tw_load<R0>(w, twA, sub);
         __syncthreads();
         if (next < io.nunits) {
             const OlsColIO::Ctx cn = io.begin(next);
 #pragma unroll 1
             for (int t = sub; t < 256; t += kOlsThreads) {
-                ols_pass_a_inv<R0, F>(sx, X, t, twA, io, ctx);
+                ols_pass_a_inv<R0, F>(sx, X, t, t + kOlsThreads, twA, w, io, ctx);
                 ols_col_fetch<R0>(io, cn, sx, X, t);       // same slots, same thread: no barrier needed
             }
         } else {
 #pragma unroll 1
-            for (int t = sub; t < 256; t += kOlsThreads) ols_pass_a_inv<R0, F>(sx, X, t, twA, io, ctx);
+            for (int t = sub; t < 256; t += kOlsThreads) ols_pass_a_inv<R0, F>(sx, X, t, t + kOlsThreads, twA, w, io, ctx);
         }
         cp_async_commit();
     }

@@ -1,9 +1,15 @@
 """Single large image sharded over the GPUs of one box.
 
-Row pass on row stripes, one all-to-all of the float32 intermediate (the distributed form of the
-reference's flip_block, Source.cpp:540), column pass on column stripes.  One process per GPU,
-torch.distributed for the exchange (NCCL over NVLink on GPUs; gloo in the CPU tests, where the two
-passes are supplied by the test as callables).
+Row pass on row stripes, one exchange of the float32 intermediate (the distributed form of the
+reference's flip_block, Source.cpp:540), column pass on column stripes.  One process per GPU.
+
+On GPUs the exchange is FUSED into the row-pass kernel: every rank's receive buffer lives in
+symmetric memory (torch.distributed._symmetric_memory: CUDA peer mappings over NVLink/NVSwitch),
+and the kernel's epilogue stores each result directly into the buffer of the rank that owns its
+column (blur_b200_gauss_row_pass_peer).  The transfer overlaps the FFTs block by block; no staging
+copy in HBM, no collective on the data path — two device-side barriers per blur order the ranks.
+Fallback (`fused=False`, or symmetric memory unavailable): a local Q buffer + NCCL all_to_all.
+The CPU tests run the same host logic over gloo with the two passes supplied as callables.
 
 Layout contract (blur_b200_gauss_shard_geometry in include/blur_b200.h):
     algorithm 0 (full-length FFT per line)   q_send [nranks][3][cpp][stripe_rows][2]
@@ -81,17 +87,35 @@ class ShardedGaussBlur:
     `col_pass(q_recv, out_cols)` default to the CUDA plan; tests may inject CPU stand-ins."""
 
     def __init__(self, rows: int, cols: int, sigma: float, nyquist_mode: int = 0, group=None,
-                 device: torch.device | None = None, row_pass=None, col_pass=None):
+                 device: torch.device | None = None, row_pass=None, col_pass=None, fused: bool | None = None):
         self.group = group
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.nranks = dist.get_world_size(group) if dist.is_initialized() else 1
         self.geom = ShardGeometry(rows, cols, self.nranks, self.rank, sigma, nyquist_mode)
         self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
         g = self.geom
-        self.q_send = torch.zeros(self.nranks * g.block_floats, dtype=torch.float32, device=self.device)
-        self.q_recv = torch.zeros_like(self.q_send)
-        self.out_cols = torch.zeros((rows, 2 * g.cpp, 3), dtype=torch.uint8, device=self.device)
+        nfl = self.nranks * g.block_floats
         self.plan = None
+        self.symm = None
+        self.q_send = None
+        want_fused = (fused is not False and row_pass is None and col_pass is None and self.nranks > 1
+                      and self.nranks <= 8 and g.algo == 1 and self.device.type == "cuda")
+        if want_fused:
+            try:
+                import torch.distributed._symmetric_memory as symm_mem
+                self.q_recv = symm_mem.empty(nfl, dtype=torch.float32, device=self.device)
+                self.q_recv.zero_()
+                self.symm = symm_mem.rendezvous(self.q_recv, group if group is not None else dist.group.WORLD)
+                self.peer_ptrs = [int(p) for p in self.symm.buffer_ptrs]
+            except Exception as e:                      # noqa: BLE001
+                if fused is True:
+                    raise
+                self.symm = None
+                self.fused_error = repr(e)
+        if self.symm is None:
+            self.q_send = torch.zeros(nfl, dtype=torch.float32, device=self.device)
+            self.q_recv = torch.zeros_like(self.q_send)
+        self.out_cols = torch.zeros((rows, 2 * g.cpp, 3), dtype=torch.uint8, device=self.device)
         if row_pass is None or col_pass is None:
             from .api import GaussPlan
             self.plan = GaussPlan(rows, cols, sigma, nyquist_mode, device=self.device.index or 0,
@@ -100,11 +124,22 @@ class ShardedGaussBlur:
             col_pass = self.plan.col_pass
         self._row_pass, self._col_pass = row_pass, col_pass
 
+    @property
+    def fused(self) -> bool:
+        return self.symm is not None
+
     def run(self, in_stripe: torch.Tensor) -> torch.Tensor:
         """in_stripe: uint8 [valid_rows, cols, 3] (this rank's rows).  Returns this rank's column
         stripe of the result, uint8 [rows, valid_cols, 3] (a view into an internal buffer)."""
-        if self.geom.valid_rows > 0:
-            self._row_pass(in_stripe, self.q_send)
-        exchange(self.q_send, self.q_recv, self.group, self.geom.algo)
+        if self.symm is not None:
+            # peers may still be reading their buffers (previous blur's column pass)
+            self.symm.barrier(channel=0)
+            if self.geom.valid_rows > 0:
+                self.plan.row_pass_peer(in_stripe, self.peer_ptrs)
+            self.symm.barrier(channel=1)                 # every rank's stores have landed
+        else:
+            if self.geom.valid_rows > 0:
+                self._row_pass(in_stripe, self.q_send)
+            exchange(self.q_send, self.q_recv, self.group, self.geom.algo)
         self._col_pass(self.q_recv, self.out_cols)
         return self.out_cols[:, : self.geom.valid_cols]

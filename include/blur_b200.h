@@ -113,6 +113,16 @@ int blur_b200_gauss_u8c3(uint8_t *h_bgr, int rows, int cols, double sigma, int n
 int blur_b200_gauss_row_pass(blur_b200_plan *plan, const uint8_t *d_in_stripe, float *d_q, void *stream);
 int blur_b200_gauss_col_pass(blur_b200_plan *plan, const float *d_q_chunks, uint8_t *d_out_cols, void *stream);
 
+/* Row pass with the exchange fused into its epilogue (overlap-save plans, nranks <= 8): q_peers[r]
+ * is the address, mapped into THIS process (CUDA IPC / symmetric memory over NVLink), of rank r's
+ * receive buffer (nranks * info[8] floats, the layout d_q_chunks of the column pass expects).  Every
+ * result is stored straight into the buffer of the rank that owns its column, as block `rank`;
+ * nothing is staged in local HBM and no collective runs.  The caller synchronises the ranks
+ * (all row passes finished) before any column pass reads its buffer, and again before the next
+ * row pass overwrites it.  Returns BLUR_B200_ESIZE for plans that use the full-length algorithm. */
+int blur_b200_gauss_row_pass_peer(blur_b200_plan *plan, const uint8_t *d_in_stripe, float *const *q_peers, int npeers,
+                                  void *stream);
+
 /* Parity hook: the float32 row-pass result (`resf` of Source.cpp:536) as planar [3][rows][cols]. */
 int blur_b200_gauss_rowpass_f32(blur_b200_plan *plan, const uint8_t *d_in, float *d_planar, void *stream);
 

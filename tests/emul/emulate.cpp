@@ -91,7 +91,8 @@ static void ols_row_units(const OlsRowIO& io, const OlsTables& T)
                 for (int it = 0; it < 16 * R0; ++it) ols_pass_b<false, 1>(s, it, T.twB.data());
                 for (int it = 0; it < 16 * R0; ++it) ols_mid<R0, 1>(s, it, T.kt.data());
                 for (int it = 0; it < 16 * R0; ++it) ols_pass_b<true, 1>(s, it, T.twB.data());
-                for (int t = 0; t < 256; ++t) ols_pass_a_inv<R0, 1>(s, ch, t, T.twA.data(), io, ctx);
+                { cplx w[R0]; ols_tw_load<R0>(w, T.twA.data(), 0);
+                  for (int t = 0; t < 256; ++t) ols_pass_a_inv<R0, 1>(s, ch, t, t + 1, T.twA.data(), w, io, ctx); }
             }
         }
     }
@@ -123,20 +124,22 @@ static void ols_col_units(const OlsColIO& io, const OlsTables& T)
                 for (int it = 0; it < 16 * R0; ++it) ols_pass_b<false, F>(sx, it, T.twB.data());
                 for (int it = 0; it < 16 * R0; ++it) ols_mid<R0, F>(sx, it, T.kt.data());
                 for (int it = 0; it < 16 * R0; ++it) ols_pass_b<true, F>(sx, it, T.twB.data());
-                for (int t = 0; t < 256; ++t) ols_pass_a_inv<R0, F>(sx, X, t, T.twA.data(), io, ctx);
+                { cplx w[R0]; ols_tw_load<R0>(w, T.twA.data(), 0);
+                  for (int t = 0; t < 256; ++t) ols_pass_a_inv<R0, F>(sx, X, t, t + 1, T.twA.data(), w, io, ctx); }
             }
         }
     }
 }
 
 static int ols_row_pass(const uint8_t* in_stripe, float* q, const GaussGeometry& gg, const ShardGeom& sg, double sigma,
-                        int nranks)
+                        int nranks, float* const* qpeer = nullptr, int rank = 0)
 {
     if (sg.valid_rows <= 0) return 0;
     OlsRowIO io{};
     io.in = in_stripe; io.q = q; io.rows = sg.valid_rows; io.cols = gg.cols; io.npairs = (sg.valid_rows + 1) / 2;
     io.srows = sg.stripe_rows; io.qpitch = sg.qpitch; io.cpart = sg.cpart; io.nparts = nranks;
     io.ax = sg.ols_row; io.nunits = io.ax.nblocks * io.npairs;
+    if (qpeer) { io.peer = 1; io.rank = rank; for (int p = 0; p < nranks; ++p) io.qpeer[p] = qpeer[p]; }
     const OlsTables T(io.ax.R0, sigma, gg.ksize);
 #define F_(R) ols_row_units<R>(io, T)
     OLS_R0_SWITCH(io.ax.R0, F_)
@@ -177,12 +180,32 @@ int emul_ols_gauss(const uint8_t* in, uint8_t* out, int rows, int cols, double s
 {
     const GaussGeometry gg = gauss_geometry(rows, cols, sigma);
     if (gg.pad < 0 || gg.pad > rows - 1 || gg.pad > cols - 1) return 2;
-    const int P = nparts;
+    const bool peer = nparts < 0;          // negative: fused exchange (row pass stores into the owners' buffers)
+    const int P = peer ? -nparts : nparts;
     std::vector<ShardGeom> sg;
     for (int r = 0; r < P; ++r) sg.push_back(shard_geometry(gg, 0, r, P));
     if (sg[0].algo != 1) return 4;
     if (info) { info[0] = sg[0].ols_row.L; info[1] = sg[0].ols_col.L; info[2] = sg[0].ols_row.nblocks; info[3] = sg[0].ols_col.nblocks; }
     const size_t bf = sg[0].block_floats, chf = bf / 3;      // floats per (stripe, part) block / per channel of it
+    if (peer) {
+        std::vector<std::vector<float>> recv(P, std::vector<float>(bf * P, 0.f));
+        std::vector<float*> ptrs;
+        for (auto& v : recv) ptrs.push_back(v.data());
+        for (int r = 0; r < P; ++r)
+            ols_row_pass(in + static_cast<size_t>(sg[r].row0) * cols * 3, nullptr, gg, sg[r], sigma, P, ptrs.data(), r);
+        for (int p = 0; p < P; ++p) {
+            std::vector<uint8_t> oc(static_cast<size_t>(rows) * 2 * sg[p].cpp * 3, 0);
+            ols_col_pass(recv[p].data(), oc.data(), gg, sg[p], sigma, p, P);
+            for (int r = 0; r < rows; ++r)
+                for (int c = 0; c < 2 * sg[p].cpp; ++c) {
+                    const int x = p * 2 * sg[p].cpp + c;
+                    if (x >= cols) continue;
+                    for (int ch = 0; ch < 3; ++ch)
+                        out[(static_cast<size_t>(r) * cols + x) * 3 + ch] = oc[(static_cast<size_t>(r) * 2 * sg[p].cpp + c) * 3 + ch];
+                }
+        }
+        return 0;
+    }
     std::vector<std::vector<float>> send(P, std::vector<float>(bf * P, 0.f));
     for (int r = 0; r < P; ++r)
         ols_row_pass(in + static_cast<size_t>(sg[r].row0) * cols * 3, send[r].data(), gg, sg[r], sigma, P);
