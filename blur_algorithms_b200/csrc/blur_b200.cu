@@ -883,6 +883,61 @@ int blur_b200_reflect_101_u8_host(const uint8_t* h_in, uint8_t* h_out, int top, 
     return rc;
 }
 
+// Host-buffer forms of the layout helpers: the reference's own signatures take host pointers
+// (Utils.hpp:159-210, flip_block call sites Source.cpp:367,384,540,562).
+namespace {
+struct DevBuf {
+    void* p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    int alloc(size_t n) { return cudaMalloc(&p, n ? n : 1) == cudaSuccess ? 0 : BLUR_B200_ECUDA; }
+};
+}  // namespace
+
+int blur_b200_deinterleave_u8_f32_host(const uint8_t* h_in, float* h_b, float* h_g, float* h_r, uint32_t total)
+{
+    if (!h_in || !h_b || !h_g || !h_r) return BLUR_B200_EINVAL;
+    if (!total) return BLUR_B200_OK;
+    DevBuf in, pl;
+    const size_t n = total;
+    if (in.alloc(3 * n) || pl.alloc(3 * n * sizeof(float))) { g_cuda_err = "cudaMalloc"; return BLUR_B200_ECUDA; }
+    float* f = static_cast<float*>(pl.p);
+    CU_TRY(cudaMemcpy(in.p, h_in, 3 * n, cudaMemcpyHostToDevice));
+    int rc = blur_b200_deinterleave_u8_f32(static_cast<const uint8_t*>(in.p), f, f + n, f + 2 * n, total, nullptr);
+    if (rc) return rc;
+    float* dst[3] = {h_b, h_g, h_r};
+    for (int c = 0; c < 3; ++c) CU_TRY(cudaMemcpy(dst[c], f + c * n, n * sizeof(float), cudaMemcpyDeviceToHost));
+    return BLUR_B200_OK;
+}
+
+int blur_b200_interleave_f32_u8_host(const float* h_b, const float* h_g, const float* h_r, uint8_t* h_out, uint32_t total)
+{
+    if (!h_out || !h_b || !h_g || !h_r) return BLUR_B200_EINVAL;
+    if (!total) return BLUR_B200_OK;
+    DevBuf out, pl;
+    const size_t n = total;
+    if (out.alloc(3 * n) || pl.alloc(3 * n * sizeof(float))) { g_cuda_err = "cudaMalloc"; return BLUR_B200_ECUDA; }
+    float* f = static_cast<float*>(pl.p);
+    const float* src[3] = {h_b, h_g, h_r};
+    for (int c = 0; c < 3; ++c) CU_TRY(cudaMemcpy(f + c * n, src[c], n * sizeof(float), cudaMemcpyHostToDevice));
+    int rc = blur_b200_interleave_f32_u8(f, f + n, f + 2 * n, static_cast<uint8_t*>(out.p), total, nullptr);
+    if (rc) return rc;
+    CU_TRY(cudaMemcpy(h_out, out.p, 3 * n, cudaMemcpyDeviceToHost));
+    return BLUR_B200_OK;
+}
+
+int blur_b200_flip_block_f32_host(const float* h_in, float* h_out, int w, int h)
+{
+    if (!h_in || !h_out || w < 1 || h < 1) return BLUR_B200_EINVAL;
+    DevBuf a, b;
+    const size_t nbytes = static_cast<size_t>(w) * h * sizeof(float);
+    if (a.alloc(nbytes) || b.alloc(nbytes)) { g_cuda_err = "cudaMalloc"; return BLUR_B200_ECUDA; }
+    CU_TRY(cudaMemcpy(a.p, h_in, nbytes, cudaMemcpyHostToDevice));
+    int rc = blur_b200_flip_block_f32(static_cast<const float*>(a.p), static_cast<float*>(b.p), w, h, nullptr);
+    if (rc) return rc;
+    CU_TRY(cudaMemcpy(h_out, b.p, nbytes, cudaMemcpyDeviceToHost));
+    return BLUR_B200_OK;
+}
+
 uint64_t blur_b200_kernel_launches(void) { return g_launches.load(); }
 void blur_b200_count_launches(uint64_t n) { g_launches += n; }
 

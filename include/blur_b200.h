@@ -148,6 +148,11 @@ int blur_b200_deinterleave_u8_f32(const uint8_t *d_in, float *d_b, float *d_g, f
 int blur_b200_interleave_f32_u8(const float *d_b, const float *d_g, const float *d_r, uint8_t *d_out, uint32_t total, void *stream);
 /* flip_block<float,1>(in,out,w,h): in is h x w, out is w x h (call sites Source.cpp:540,562) */
 int blur_b200_flip_block_f32(const float *d_in, float *d_out, int w, int h, void *stream);
+/* the same three on HOST buffers (H2D + kernel + D2H): the pointer kinds of the reference's own
+ * signatures (Utils.hpp:159-160,186-187; flip_block call sites Source.cpp:367,384,540,562) */
+int blur_b200_deinterleave_u8_f32_host(const uint8_t *h_in, float *h_b, float *h_g, float *h_r, uint32_t total);
+int blur_b200_interleave_f32_u8_host(const float *h_b, const float *h_g, const float *h_r, uint8_t *h_out, uint32_t total);
+int blur_b200_flip_block_f32_host(const float *h_in, float *h_out, int w, int h);
 
 /* ---- DFT_image spectrum path (pocketfft_2D with #define DFT_image, Source.cpp:240-252) ------- */
 /* d_in uint8 [rows][cols][3]; d_out uint8 [rows][cols][3] spectrum image; optional d_spec_f32
