@@ -201,7 +201,9 @@ def main() -> None:
         plan = bb.GaussPlan(rows, cols, sigma, bb.NYQUIST_EXACT, device=local)
         step = lambda: plan.run(d_in, d_out)            # noqa: E731
     else:
-        sb = ShardedGaussBlur(rows, cols, sigma, bb.NYQUIST_EXACT, device=dev)
+        fused_env = os.environ.get("BLUR_B200_FUSED")        # "0": NCCL all_to_all exchange instead of the fused peer stores
+        sb = ShardedGaussBlur(rows, cols, sigma, bb.NYQUIST_EXACT, device=dev,
+                              fused=None if fused_env is None else fused_env != "0")
         g = sb.geom
         # every rank draws the same image stream and keeps its stripe
         full_rng = np.random.default_rng(0)
@@ -217,8 +219,13 @@ def main() -> None:
         h_img = torch.from_numpy(stripe_np).pin_memory()
         d_in = h_img.to(dev)
         plan = sb.plan
-        config["exchange"] = ("fused: row-pass epilogue stores into the owners' symmetric-memory buffers over NVLink"
-                              if sb.fused else "NCCL all_to_all of the float32 intermediate")
+        if not sb.fused:
+            config["exchange"] = "NCCL all_to_all of the float32 intermediate"
+        elif sb.exchange_mode == "store":
+            config["exchange"] = "fused: row-pass epilogue stores into the owners' symmetric-memory buffers over NVLink"
+        else:
+            config["exchange"] = (f"pipelined: row pass in {sb.nchunks} chunks, q_push_kernel copies each finished chunk into the "
+                                  "owners' symmetric-memory buffers over NVLink (128-bit peer stores) under the next chunk's FFTs")
         step = lambda: sb.run(d_in)                      # noqa: E731
 
     # ---- device-resident timing
@@ -268,7 +275,12 @@ def main() -> None:
         del q, oc
     else:
         g = sb.geom
-        rp = (lambda: sb.plan.row_pass_peer(d_in, sb.peer_ptrs)) if sb.fused else (lambda: sb.plan.row_pass(d_in, sb.q_send))
+        if not sb.fused:
+            rp = lambda: sb.plan.row_pass(d_in, sb.q_send)                                   # noqa: E731
+        elif sb.exchange_mode == "store":
+            rp = lambda: sb.plan.row_pass_peer(d_in, sb.peer_ptrs)                           # noqa: E731
+        else:
+            rp = lambda: sb.plan.row_pass_push(d_in, sb.peer_ptrs, sb.nchunks)               # noqa: E731
         barrier()
         rp(); sb.plan.col_pass(sb.q_recv, sb.out_cols)
         barrier()

@@ -164,6 +164,13 @@ class GaussPlan:
         check(lib.blur_b200_gauss_row_pass_peer(self._h, _ptr(d_in_stripe), arr, len(q_peer_ptrs),
                                                 _stream() if stream is None else stream))
 
+    def row_pass_push(self, d_in_stripe, q_peer_ptrs, nchunks: int = 4, stream: int | None = None):
+        """Row pass in `nchunks` groups of row pairs, each pushed to the owners' receive buffers by a
+        copy kernel over NVLink while the next group is transformed (pipelined exchange)."""
+        arr = (C.c_void_p * len(q_peer_ptrs))(*[int(p) for p in q_peer_ptrs])
+        check(lib.blur_b200_gauss_row_pass_push(self._h, _ptr(d_in_stripe), arr, len(q_peer_ptrs), int(nchunks),
+                                                _stream() if stream is None else stream))
+
     def col_pass(self, d_q_chunks, d_out_cols, stream: int | None = None):
         check(lib.blur_b200_gauss_col_pass(self._h, _ptr(d_q_chunks), _ptr(d_out_cols), _stream() if stream is None else stream))
 

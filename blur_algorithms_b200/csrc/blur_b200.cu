@@ -222,6 +222,37 @@ __global__ void transpose_f32_kernel(const float* __restrict__ in, float* __rest
     }
 }
 
+// ------------------------------------------------------------------ exchange kernel
+// The distributed flip_block (Source.cpp:540) of the sharded plan: after a chunk of row pairs has
+// been transformed into the local send buffer, this kernel pushes the blocks owned by the other
+// GPUs into their receive buffers through NVLink peer mappings with 128-bit stores, while the row
+// pass of the next chunk runs on the compute stream.  One segment = rows [r0, r1) of one
+// (channel, destination) block: contiguous on both sides.
+struct PushArgs {
+    static constexpr int kMaxSeg = 3 * 7;
+    const float4* src[kMaxSeg];
+    float4* dst[kMaxSeg];
+    int nseg;
+    unsigned n4;                 // float4 per segment
+};
+
+__global__ void __launch_bounds__(256)
+q_push_kernel(const __grid_constant__ PushArgs a)
+{
+    const unsigned stride = gridDim.x * 256u;
+    for (int s = blockIdx.y; s < a.nseg; s += gridDim.y) {
+        const float4* __restrict__ src = a.src[s];
+        float4* __restrict__ dst = a.dst[s];
+        unsigned i = blockIdx.x * 256u + threadIdx.x;
+        for (; i + 3 * stride < a.n4; i += 4 * stride) {           // four loads in flight per thread
+            const float4 v0 = __ldcs(src + i), v1 = __ldcs(src + i + stride);
+            const float4 v2 = __ldcs(src + i + 2 * stride), v3 = __ldcs(src + i + 3 * stride);
+            dst[i] = v0; dst[i + stride] = v1; dst[i + 2 * stride] = v2; dst[i + 3 * stride] = v3;
+        }
+        for (; i < a.n4; i += stride) dst[i] = __ldcs(src + i);
+    }
+}
+
 // ------------------------------------------------------------------ box blur kernels
 // Declared semantics: out = (2*sum + k) / (2k), sum over the reflect-101 window.
 
@@ -383,6 +414,12 @@ struct blur_b200_plan {
     float* d_q_recv = nullptr;        // unused on a single GPU
     int num_sms = 148;
     cudaStream_t stream = nullptr;
+    cudaStream_t push_stream = nullptr;            // exchange kernels of the sharded plan
+    static constexpr int kMaxChunks = 16;
+    cudaEvent_t ev_chunk[kMaxChunks] = {};
+    cudaEvent_t ev_pushed = nullptr;
+    cudaStream_t ce_stream[7] = {};                // one per destination GPU: copies to different peers run on different engines
+    cudaEvent_t ev_ce[7] = {};
 };
 
 namespace {
@@ -646,6 +683,11 @@ void blur_b200_gauss_plan_destroy(blur_b200_plan* p)
     cudaFree(p->d_ols_kt_row); cudaFree(p->d_ols_kt_col);
     cudaFree(p->d_q); cudaFree(p->d_u); cudaFree(p->d_io);
     if (p->stream) cudaStreamDestroy(p->stream);
+    if (p->push_stream) cudaStreamDestroy(p->push_stream);
+    for (cudaEvent_t e : p->ev_chunk) if (e) cudaEventDestroy(e);
+    if (p->ev_pushed) cudaEventDestroy(p->ev_pushed);
+    for (cudaStream_t cs : p->ce_stream) if (cs) cudaStreamDestroy(cs);
+    for (cudaEvent_t e : p->ev_ce) if (e) cudaEventDestroy(e);
     delete p;
 }
 
@@ -721,6 +763,106 @@ int blur_b200_gauss_row_pass_peer(blur_b200_plan* p, const uint8_t* d_in_stripe,
     for (int k = 0; k < npeers; ++k)
         if (!q_peers[k]) return BLUR_B200_EINVAL;
     return run_row_pass(p, d_in_stripe, p->d_q, static_cast<cudaStream_t>(stream), q_peers);
+}
+
+int blur_b200_gauss_row_pass_push(blur_b200_plan* p, const uint8_t* d_in_stripe, float* const* q_peers, int npeers,
+                                  int nchunks, void* stream)
+{
+    if (!p || !d_in_stripe || !q_peers || npeers != p->nranks || npeers > OlsRowIO::kMaxPeers) return BLUR_B200_EINVAL;
+    if (p->algo != 1) return BLUR_B200_ESIZE;
+    for (int k = 0; k < npeers; ++k)
+        if (!q_peers[k]) return BLUR_B200_EINVAL;
+    if (p->valid_rows <= 0) return BLUR_B200_OK;
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int N = p->nranks, rank = p->rank;
+    if (!p->push_stream) {
+        int prio_lo = 0, prio_hi = 0;
+        CU_TRY(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+        CU_TRY(cudaStreamCreateWithPriority(&p->push_stream, cudaStreamNonBlocking, prio_hi));
+        // Same shared-memory carveout as the row kernel, or the two cannot share an SM: the copy
+        // CTAs must slip in beside the resident FFT CTAs of the next chunk.
+        CU_TRY(cudaFuncSetAttribute(q_push_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        for (cudaEvent_t& e : p->ev_chunk) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        CU_TRY(cudaEventCreateWithFlags(&p->ev_pushed, cudaEventDisableTiming));
+        for (int d = 0; d + 1 < N; ++d) {
+            CU_TRY(cudaStreamCreateWithPriority(&p->ce_stream[d], cudaStreamNonBlocking, prio_hi));
+            CU_TRY(cudaEventCreateWithFlags(&p->ev_ce[d], cudaEventDisableTiming));
+        }
+    }
+    const int npairs = cdiv(p->valid_rows, 2);
+    nchunks = std::max(1, std::min({nchunks, static_cast<int>(blur_b200_plan::kMaxChunks), npairs}));
+    const size_t blk = static_cast<size_t>(p->stripe_rows) * p->qpitch;        // floats per (channel, part) block
+    // Row kernel in "peer" addressing (ols_core.cuh): part == rank lands in our own receive buffer as
+    // block (ch, rank); every other part lands in the local send buffer d_q as block (ch, part).
+    float* base[OlsRowIO::kMaxPeers];
+    for (int part = 0; part < N; ++part)
+        base[part] = part == rank ? q_peers[rank] : p->d_q + (static_cast<ptrdiff_t>(part) - rank) * static_cast<ptrdiff_t>(blk);
+    // Chunks are whole waves of the persistent row grid (grid CTAs / blocks per line row pairs), so
+    // cutting the stripe adds no partially filled wave except the stripe's own last one.
+    const int wave_pairs = std::max(1, p->num_sms * ols_resident_ctas(p->ols_row.R0) / std::max(1, p->ols_row.nblocks));
+    const int nwaves = cdiv(npairs, wave_pairs);
+    nchunks = std::min(nchunks, nwaves);
+    for (int c = 0; c < nchunks; ++c) {
+        const int p0 = std::min(npairs, static_cast<int>(static_cast<int64_t>(nwaves) * c / nchunks) * wave_pairs);
+        const int p1 = c + 1 == nchunks ? npairs : std::min(npairs, static_cast<int>(static_cast<int64_t>(nwaves) * (c + 1) / nchunks) * wave_pairs);
+        const int r0 = 2 * p0, r1 = std::min(2 * p1, p->valid_rows);
+        if (r1 <= r0) continue;
+        OlsRowIO io{};
+        io.in = d_in_stripe + static_cast<size_t>(r0) * p->cols * 3;
+        io.q = p->d_q;
+        io.rows = r1 - r0; io.cols = p->cols;
+        io.npairs = cdiv(io.rows, 2);
+        io.srows = p->stripe_rows; io.qpitch = p->qpitch; io.cpart = p->cpart; io.nparts = N;
+        io.ax = p->ols_row;
+        io.nunits = io.ax.nblocks * io.npairs;
+        io.peer = 1; io.rank = rank;
+        for (int part = 0; part < N; ++part) io.qpeer[part] = base[part] + static_cast<size_t>(r0) * p->qpitch;
+        static const int diag = std::getenv("BLUR_B200_PUSH_DIAG") ? std::atoi(std::getenv("BLUR_B200_PUSH_DIAG")) : 0;   // timing experiments only
+        if (diag != 1) {
+            static const int sms_free = std::getenv("BLUR_B200_ROW_SMS_FREE") ? std::atoi(std::getenv("BLUR_B200_ROW_SMS_FREE")) : 0;
+            CU_TRY(launch_ols_row(io, p->d_ols_twa_row, p->d_ols_twb, p->d_ols_kt_row, p->num_sms - (N > 1 ? sms_free : 0), st));
+            ++g_launches;
+        }
+        if (N == 1 || diag == 2) continue;
+        CU_TRY(cudaEventRecord(p->ev_chunk[c], st));
+        CU_TRY(cudaStreamWaitEvent(p->push_stream, p->ev_chunk[c], 0));
+        PushArgs a{};
+        a.n4 = static_cast<unsigned>(static_cast<size_t>(r1 - r0) * p->qpitch / 4);
+        for (int d = 1; d < N; ++d) {                       // start with the next rank: spread the NVSwitch ports
+            const int part = (rank + d) % N;
+            for (int ch = 0; ch < 3; ++ch) {
+                a.src[a.nseg] = reinterpret_cast<const float4*>(p->d_q + (static_cast<size_t>(ch) * N + part) * blk + static_cast<size_t>(r0) * p->qpitch);
+                a.dst[a.nseg] = reinterpret_cast<float4*>(q_peers[part] + (static_cast<size_t>(ch) * N + rank) * blk + static_cast<size_t>(r0) * p->qpitch);
+                ++a.nseg;
+            }
+        }
+        // Default: the GPU's copy engines move the segments (one contiguous peer copy each) — measured on
+        // B200 they run fully underneath the next chunk's FFT kernel at ~700 GB/s, while q_push_kernel
+        // (BLUR_B200_PUSH_ENGINE=sm) reaches the same rate alone but does not overlap the resident
+        // persistent row grid (profiles/r01_exchange_modes.txt).
+        static const int use_ce = !(std::getenv("BLUR_B200_PUSH_ENGINE") && !std::strcmp(std::getenv("BLUR_B200_PUSH_ENGINE"), "sm"));
+        if (use_ce) {
+            for (int sgm = 0; sgm < a.nseg; ++sgm) {          // segments are ordered destination-major, 3 channels each
+                cudaStream_t cs = p->ce_stream[sgm / 3];
+                if (sgm % 3 == 0) CU_TRY(cudaStreamWaitEvent(cs, p->ev_chunk[c], 0));
+                CU_TRY(cudaMemcpyAsync(a.dst[sgm], a.src[sgm], static_cast<size_t>(a.n4) * 16, cudaMemcpyDeviceToDevice, cs));
+            }
+        } else {
+            const int gx = std::max(1, std::min<int>(cdiv(static_cast<int>(a.n4), 256 * 4), std::max(1, 2 * p->num_sms / a.nseg)));
+            q_push_kernel<<<dim3(gx, a.nseg), 256, 0, p->push_stream>>>(a);
+            CU_TRY(cudaGetLastError());
+            ++g_launches;
+        }
+    }
+    if (N > 1) {
+        CU_TRY(cudaEventRecord(p->ev_pushed, p->push_stream));
+        CU_TRY(cudaStreamWaitEvent(st, p->ev_pushed, 0));
+        for (int d = 0; d + 1 < N; ++d) {
+            CU_TRY(cudaEventRecord(p->ev_ce[d], p->ce_stream[d]));
+            CU_TRY(cudaStreamWaitEvent(st, p->ev_ce[d], 0));
+        }
+    }
+    return BLUR_B200_OK;
 }
 
 int blur_b200_gauss_col_pass(blur_b200_plan* p, const float* d_q_chunks, uint8_t* d_out_cols, void* stream)

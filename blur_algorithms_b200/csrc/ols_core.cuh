@@ -243,6 +243,7 @@ struct OlsRowIO {
         int s;               // extended-line position of tile index 0
         int w0, w1;          // staged source pixels [w0, w1)
         int nvalid;          // outputs this block keeps: tile indices [halo, halo + nvalid)
+        int part0, b1;       // nparts > 1: part of the block's first output column, first column of part0 + 1
         bool has_b, interior;
     };
     BLUR_HD Stage stage_of(int row, int s, int w0, int w1) const
@@ -270,6 +271,8 @@ struct OlsRowIO {
         c.w1 = c.s + ax.L < cols ? c.s + ax.L : cols;
         c.nvalid = cols - b * ax.V < ax.V ? cols - b * ax.V : ax.V;
         c.interior = c.s >= 0 && c.s + ax.L <= cols;
+        c.part0 = nparts > 1 ? (b * ax.V) / cpart : 0;
+        c.b1 = (c.part0 + 1) * cpart;
         c.ia = stage_of(c.ra, c.s, c.w0, c.w1).b0;
         c.ib = c.has_b ? raw_pitch + stage_of(c.ra + 1, c.s, c.w0, c.w1).b0 : c.ia;
         return c;
@@ -322,6 +325,27 @@ struct OlsRowIO {
 #pragma unroll
             for (int j = 0; j < R0; ++j) {
                 const bool va = j >= jlo && j <= jhi, vb = va && c.has_b;
+                if (va) d[256 * j] = cre(x[j]);
+                if (vb) d[qpitch + 256 * j] = cim(x[j]);
+            }
+        } else if (ax.V <= 2 * cpart) {
+            // The block's outputs start in part0 and span at most V <= 2*cpart columns, so an item's
+            // elements fall in at most three parts: three base pointers per item, then every
+            // element is a select between them plus an immediate offset (no division, no 64-bit
+            // address arithmetic per element).
+            const size_t rowoff = peer ? (static_cast<size_t>(X * nparts + rank) * srows + c.ra) * qpitch : 0;
+            float* pp[3];
+#pragma unroll
+            for (int k = 0; k < 3; ++k) {
+                const int part = c.part0 + k < nparts ? c.part0 + k : nparts - 1;
+                float* b = peer ? qpeer[part] + rowoff : qc + static_cast<size_t>(part) * srows * qpitch;
+                pp[k] = b + (static_cast<ptrdiff_t>(x0) - static_cast<ptrdiff_t>(part) * cpart);   // element x0 + 256 j lives at pp[k] + 256 j
+            }
+            const int e1 = c.b1 - x0, e2 = e1 + cpart;         // 256 j >= e1: part0 + 1 ; >= e2: part0 + 2
+#pragma unroll
+            for (int j = 0; j < R0; ++j) {
+                const bool va = j >= jlo && j <= jhi, vb = va && c.has_b;
+                float* d = 256 * j >= e2 ? pp[2] : (256 * j >= e1 ? pp[1] : pp[0]);
                 if (va) d[256 * j] = cre(x[j]);
                 if (vb) d[qpitch + 256 * j] = cim(x[j]);
             }

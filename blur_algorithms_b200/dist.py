@@ -20,6 +20,7 @@ rank's column stripe [rows][2*cpp][3] uint8.
 from __future__ import annotations
 
 import ctypes as C
+import os
 from dataclasses import dataclass
 
 import torch
@@ -87,7 +88,8 @@ class ShardedGaussBlur:
     `col_pass(q_recv, out_cols)` default to the CUDA plan; tests may inject CPU stand-ins."""
 
     def __init__(self, rows: int, cols: int, sigma: float, nyquist_mode: int = 0, group=None,
-                 device: torch.device | None = None, row_pass=None, col_pass=None, fused: bool | None = None):
+                 device: torch.device | None = None, row_pass=None, col_pass=None, fused: bool | None = None,
+                 exchange_mode: str | None = None, nchunks: int | None = None):
         self.group = group
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.nranks = dist.get_world_size(group) if dist.is_initialized() else 1
@@ -97,6 +99,10 @@ class ShardedGaussBlur:
         nfl = self.nranks * g.block_floats
         self.plan = None
         self.symm = None
+        # "push": row pass in chunks + copy kernel over peer mappings (default); "store": the row
+        # kernel's epilogue stores remotely itself.  BLUR_B200_EXCHANGE overrides.
+        self.exchange_mode = exchange_mode or os.environ.get("BLUR_B200_EXCHANGE", "push")
+        self.nchunks = nchunks or int(os.environ.get("BLUR_B200_CHUNKS", "0")) or max(2, 8 // max(self.nranks, 1))
         self.q_send = None
         want_fused = (fused is not False and row_pass is None and col_pass is None and self.nranks > 1
                       and self.nranks <= 8 and g.algo == 1 and self.device.type == "cuda")
@@ -135,7 +141,10 @@ class ShardedGaussBlur:
             # peers may still be reading their buffers (previous blur's column pass)
             self.symm.barrier(channel=0)
             if self.geom.valid_rows > 0:
-                self.plan.row_pass_peer(in_stripe, self.peer_ptrs)
+                if self.exchange_mode == "store":
+                    self.plan.row_pass_peer(in_stripe, self.peer_ptrs)
+                else:
+                    self.plan.row_pass_push(in_stripe, self.peer_ptrs, self.nchunks)
             self.symm.barrier(channel=1)                 # every rank's stores have landed
         else:
             if self.geom.valid_rows > 0:

@@ -123,6 +123,16 @@ int blur_b200_gauss_col_pass(blur_b200_plan *plan, const float *d_q_chunks, uint
 int blur_b200_gauss_row_pass_peer(blur_b200_plan *plan, const uint8_t *d_in_stripe, float *const *q_peers, int npeers,
                                   void *stream);
 
+/* Row pass pipelined with the exchange (overlap-save plans, nranks <= 8): the stripe is cut into
+ * `nchunks` groups of row pairs; each group is transformed into the plan's local send buffer (the
+ * part this rank owns goes straight into q_peers[rank]) and, while the next group is being
+ * transformed, a copy kernel on the plan's second stream pushes the finished group's blocks into the
+ * owners' receive buffers q_peers[r] with 128-bit stores over the NVLink peer mappings.  On return
+ * `stream` waits for every push.  Same caller-side synchronisation between ranks as
+ * blur_b200_gauss_row_pass_peer. */
+int blur_b200_gauss_row_pass_push(blur_b200_plan *plan, const uint8_t *d_in_stripe, float *const *q_peers, int npeers,
+                                  int nchunks, void *stream);
+
 /* Parity hook: the float32 row-pass result (`resf` of Source.cpp:536) as planar [3][rows][cols]. */
 int blur_b200_gauss_rowpass_f32(blur_b200_plan *plan, const uint8_t *d_in, float *d_planar, void *stream);
 
