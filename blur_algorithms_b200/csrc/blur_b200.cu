@@ -842,10 +842,14 @@ int blur_b200_gauss_row_pass_push(blur_b200_plan* p, const uint8_t* d_in_stripe,
         // persistent row grid (profiles/r01_exchange_modes.txt).
         static const int use_ce = !(std::getenv("BLUR_B200_PUSH_ENGINE") && !std::strcmp(std::getenv("BLUR_B200_PUSH_ENGINE"), "sm"));
         if (use_ce) {
-            for (int sgm = 0; sgm < a.nseg; ++sgm) {          // segments are ordered destination-major, 3 channels each
-                cudaStream_t cs = p->ce_stream[sgm / 3];
-                if (sgm % 3 == 0) CU_TRY(cudaStreamWaitEvent(cs, p->ev_chunk[c], 0));
-                CU_TRY(cudaMemcpyAsync(a.dst[sgm], a.src[sgm], static_cast<size_t>(a.n4) * 16, cudaMemcpyDeviceToDevice, cs));
+            // segments are ordered destination-major, 3 channels each at a pitch of N blocks: one
+            // 2-D copy (3 rows) per destination and chunk
+            for (int d = 0; d + 1 < N; ++d) {
+                cudaStream_t cs = p->ce_stream[d];
+                CU_TRY(cudaStreamWaitEvent(cs, p->ev_chunk[c], 0));
+                CU_TRY(cudaMemcpy2DAsync(a.dst[3 * d], static_cast<size_t>(N) * blk * sizeof(float), a.src[3 * d],
+                                         static_cast<size_t>(N) * blk * sizeof(float), static_cast<size_t>(a.n4) * 16, 3,
+                                         cudaMemcpyDeviceToDevice, cs));
             }
         } else {
             const int gx = std::max(1, std::min<int>(cdiv(static_cast<int>(a.n4), 256 * 4), std::max(1, 2 * p->num_sms / a.nseg)));
