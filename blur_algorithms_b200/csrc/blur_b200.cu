@@ -19,6 +19,11 @@
 #include "ols_launch.hpp"
 #include "ols_plan.hpp"
 
+namespace blurb200 {
+// boxblur.cu
+cudaError_t launch_box_fused_pass(const uint8_t* in, uint8_t* out, int w, int h, int C, int r, int batch, size_t img_stride,
+                                  cudaStream_t st);
+}
 using namespace blurb200;
 
 namespace {
@@ -254,6 +259,8 @@ q_push_kernel(const __grid_constant__ PushArgs a)
 }
 
 // ------------------------------------------------------------------ box blur kernels
+// The fused one-kernel-per-pass path lives in boxblur.cu; the two kernels below are the general
+// fallback (any channel count, any window that fits a row in shared memory).
 // Declared semantics: out = (2*sum + k) / (2k), sum over the reflect-101 window.
 
 struct DivK {
@@ -918,6 +925,22 @@ int blur_b200_fastboxblur_device(uint8_t* d_img, int w, int h, int channels, int
         CU_TRY(cudaFuncSetAttribute(boxblur_h_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_h)));
         configured = smem_h;
     }
+    // Fused path: one kernel per 2-D pass over the whole batch, ping-pong between image and scratch.
+    if (!std::getenv("BLUR_B200_BOX_UNFUSED")) {
+        uint8_t *src = d_img, *dst = d_scratch;
+        bool fused_ok = true;
+        for (int p = 0; p < passes; ++p) {
+            const cudaError_t e = blurb200::launch_box_fused_pass(src, dst, w, h, channels, r, batch, img_bytes, st);
+            if (e == cudaErrorNotSupported && p == 0) { fused_ok = false; break; }
+            CU_TRY(e);
+            ++g_launches;
+            std::swap(src, dst);
+        }
+        if (fused_ok) {
+            if (src != d_img) CU_TRY(cudaMemcpyAsync(d_img, src, img_bytes * batch, cudaMemcpyDeviceToDevice, st));
+            return BLUR_B200_OK;
+        }
+    }
     const int pitch = w * channels;
     const bool vec = (pitch % 4 == 0) && (reinterpret_cast<uintptr_t>(d_img) % 4 == 0) &&
                      (reinterpret_cast<uintptr_t>(d_scratch) % 4 == 0) && (img_bytes % 4 == 0);
@@ -925,6 +948,7 @@ int blur_b200_fastboxblur_device(uint8_t* d_img, int w, int h, int channels, int
     // Keep each group's image + scratch resident in L2 across the 2*passes sweeps.
     const size_t l2_budget = 48ull << 20;
     int group = static_cast<int>(std::max<size_t>(1, l2_budget / (2 * img_bytes)));
+    if (const char* e = std::getenv("BLUR_B200_BOX_GROUP")) group = std::max(1, std::atoi(e));
     group = std::min(group, 65535);
     for (int b0 = 0; b0 < batch; b0 += group) {
         const int nb = std::min(group, batch - b0);

@@ -306,8 +306,16 @@ struct OlsRowIO {
         const uint8_t* pa = c.raw + c.ia + 3 * t + X;
         const int db = c.ib - c.ia;
         if (c.has_b) {
+#ifdef __CUDA_ARCH__
+            // 0x4B000000 | b is the float 2^23 + b: bias both halves, remove it with ONE packed subtract
+            const cplx bias = cpack(8388608.f, 8388608.f);
+#pragma unroll
+            for (int j = 0; j < R0; ++j)
+                x[j] = csub(cpack(__uint_as_float(0x4B000000u | pa[768 * j]), __uint_as_float(0x4B000000u | pa[db + 768 * j])), bias);
+#else
 #pragma unroll
             for (int j = 0; j < R0; ++j) x[j] = cpack(u8f(pa[768 * j]), u8f(pa[db + 768 * j]));
+#endif
         } else {
 #pragma unroll
             for (int j = 0; j < R0; ++j) x[j] = cpack(u8f(pa[768 * j]), 0.f);
@@ -322,11 +330,21 @@ struct OlsRowIO {
         float* qc = c.qa + static_cast<size_t>(X) * nparts * srows * qpitch;
         if (nparts == 1) {
             float* d = qc + x0;
+            // halo <= 256 and a full block: elements j = 1 .. R0-2 are valid for every item, only the
+            // first and the last one depend on t
+            const bool mid_all = ax.halo <= 256 && c.nvalid == ax.V;
+            if (mid_all && c.has_b) {
+                if (jlo == 0) { d[0] = cre(x[0]); d[qpitch] = cim(x[0]); }
 #pragma unroll
-            for (int j = 0; j < R0; ++j) {
-                const bool va = j >= jlo && j <= jhi, vb = va && c.has_b;
-                if (va) d[256 * j] = cre(x[j]);
-                if (vb) d[qpitch + 256 * j] = cim(x[j]);
+                for (int j = 1; j < R0 - 1; ++j) { d[256 * j] = cre(x[j]); d[qpitch + 256 * j] = cim(x[j]); }
+                if (jhi == R0 - 1) { d[256 * (R0 - 1)] = cre(x[R0 - 1]); d[qpitch + 256 * (R0 - 1)] = cim(x[R0 - 1]); }
+            } else {
+#pragma unroll
+                for (int j = 0; j < R0; ++j) {
+                    const bool va = j >= jlo && j <= jhi, vb = va && c.has_b;
+                    if (va) d[256 * j] = cre(x[j]);
+                    if (vb) d[qpitch + 256 * j] = cim(x[j]);
+                }
             }
         } else if (ax.V <= 2 * cpart) {
             // The block's outputs start in part0 and span at most V <= 2*cpart columns, so an item's

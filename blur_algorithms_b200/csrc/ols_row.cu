@@ -1,4 +1,6 @@
 // ols_row.cu — row-pass instantiations of the overlap-save kernel.
+#include <algorithm>
+#include <cstdlib>
 #include "ols_kernels.cuh"
 #include "ols_launch.hpp"
 
@@ -15,7 +17,19 @@ static cudaError_t launch_row(const OlsRowIO& io, const float2* twA, const float
         if (e != cudaSuccess) return e;
         configured = true;
     }
-    const int grid = std::min(io.nunits, num_sms * ols_row_ctas_per_sm<R0>());
+    // experiment knob: fewer resident CTAs and a smaller shared-memory carveout leave the twiddle
+    // tables room in L1 (BLUR_B200_ROW_CTAS=4 BLUR_B200_ROW_CARVEOUT=86)
+    static const int ctas_env = std::getenv("BLUR_B200_ROW_CTAS") ? std::atoi(std::getenv("BLUR_B200_ROW_CTAS")) : 0;
+    static bool carve_done = false;
+    if (!carve_done) {
+        carve_done = true;
+        if (const char* e = std::getenv("BLUR_B200_ROW_CARVEOUT")) {
+            cudaError_t ce = cudaFuncSetAttribute(ols_row_kernel<R0>, cudaFuncAttributePreferredSharedMemoryCarveout, std::atoi(e));
+            if (ce != cudaSuccess) return ce;
+        }
+    }
+    const int per_sm = ctas_env > 0 ? std::min(ctas_env, ols_row_ctas_per_sm<R0>()) : ols_row_ctas_per_sm<R0>();
+    const int grid = std::min(io.nunits, num_sms * per_sm);
     if (grid <= 0) return cudaSuccess;
     ols_row_kernel<R0><<<grid, ols_row_threads<R0>(), smem, stream>>>(io, twA, twB, kt);
     return cudaGetLastError();
