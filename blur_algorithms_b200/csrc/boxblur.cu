@@ -34,6 +34,15 @@ __device__ __forceinline__ int box_refl(int i, int L)
     return i < 0 ? 0 : (i >= L ? L - 1 : i);          // far outside: clamped, such samples are never used
 }
 
+// acc + byte kk of `add` - byte kk of `sub`: two dp4a (unsigned bytes x signed selector bytes)
+__device__ __forceinline__ uint32_t box_acc(uint32_t acc, uint32_t add, uint32_t sub, int kk)
+{
+    int r;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(r) : "r"(add), "r"(1 << (8 * kk)), "r"(static_cast<int>(acc)));
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(r) : "r"(sub), "r"(static_cast<int>(0xFFu << (8 * kk))), "r"(r));
+    return static_cast<uint32_t>(r);
+}
+
 struct BoxTileArgs {
     const uint8_t* in;
     uint8_t* out;
@@ -66,8 +75,10 @@ boxblur_tile_kernel(const __grid_constant__ BoxTileArgs a)
         if (interior) {
             // x0b, O, wb and the image base are multiples of 4: u = 0 (mod 4) is word aligned on both sides
             const int w0 = -((-ulo + 3) & ~3);                 // ulo (negative) floored to a word
+            // asynchronous 4-byte copies: every row of the tile is in flight at once, no register staging
             for (int u = w0 + 4 * lane; u < uhi; u += 128)
-                *reinterpret_cast<uint32_t*>(srow + u + a.O) = *reinterpret_cast<const uint32_t*>(row + x0b + u);
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(srow + u + a.O))),
+                             "l"(row + x0b + u) : "memory");
         } else {
             const int x0p = x0b / C;
             for (int e = lane; e < (uhi - ulo); e += 32) {
@@ -77,6 +88,7 @@ boxblur_tile_kernel(const __grid_constant__ BoxTileArgs a)
             }
         }
     }
+    asm volatile("cp.async.commit_group;\ncp.async.wait_group 0;" ::: "memory");
     __syncthreads();
 
     // ---- horizontal pass, in place: H[b] (b in [0, TXB)) overwrites storage byte b of the row
@@ -107,7 +119,7 @@ boxblur_tile_kernel(const __grid_constant__ BoxTileArgs a)
 #pragma unroll
                 for (int kk = 0; kk < 4; ++kk) {
                     const int ph = (4 * it + kk) % C;
-                    acc[ph] = acc[ph] + ((nw >> (8 * kk)) & 255u) - ((ow >> (8 * kk)) & 255u);
+                    acc[ph] = box_acc(acc[ph], nw, ow, kk);
                     outw |= __umulhi(acc[ph], a.magic) << (8 * kk);
                 }
                 hw[wq + it] = outw;
@@ -137,7 +149,7 @@ boxblur_tile_kernel(const __grid_constant__ BoxTileArgs a)
                 const uint32_t vn = *reinterpret_cast<const uint32_t*>(col + (j + 1 + 2 * a.r) * a.pitch);
                 const uint32_t vo = *reinterpret_cast<const uint32_t*>(col + j * a.pitch);
 #pragma unroll
-                for (int kk = 0; kk < 4; ++kk) acc[kk] = acc[kk] + ((vn >> (8 * kk)) & 255u) - ((vo >> (8 * kk)) & 255u);
+                for (int kk = 0; kk < 4; ++kk) acc[kk] = box_acc(acc[kk], vn, vo, kk);
             }
         }
     }
