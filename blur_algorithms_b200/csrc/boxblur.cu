@@ -68,23 +68,27 @@ boxblur_tile_kernel(const __grid_constant__ BoxTileArgs a)
 
     // ---- load: staged byte u in [-(r+1)C, TXB + rC) of tile row ry at sm[ry*pitch + u + O]
     const int ulo = -(rC + C), uhi = kBoxTXB + rC;
-    const bool interior = x0b + ulo >= 4 && x0b + uhi + 4 <= wb;
     for (int ry = wid; ry < a.rows_t; ry += kBoxThreads / 32) {
         const uint8_t* row = img + static_cast<size_t>(box_refl(y0 - a.r + ry, a.h)) * wb;
         uint8_t* srow = sm + ry * a.pitch;
-        if (interior) {
-            // x0b, O, wb and the image base are multiples of 4: u = 0 (mod 4) is word aligned on both sides
-            const int w0 = -((-ulo + 3) & ~3);                 // ulo (negative) floored to a word
-            // asynchronous 4-byte copies: every row of the tile is in flight at once, no register staging
-            for (int u = w0 + 4 * lane; u < uhi; u += 128)
+        // u = 0 (mod 4) is word aligned on both sides (x0b, O, wb and the image base are multiples of 4).
+        // Words that lie inside the image row travel as asynchronous 4-byte copies (every row of the tile
+        // in flight at once, no register staging); only the reflected bytes of border tiles go one by one.
+        const int w0 = -((-ulo + 3) & ~3);                     // ulo (negative) floored to a word
+        const int x0p = x0b / C;
+        for (int u = w0 + 4 * lane; u < uhi; u += 128) {
+            const int gx = x0b + u;
+            if (gx >= 0 && gx + 4 <= wb) {
                 asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(static_cast<uint32_t>(__cvta_generic_to_shared(srow + u + a.O))),
-                             "l"(row + x0b + u) : "memory");
-        } else {
-            const int x0p = x0b / C;
-            for (int e = lane; e < (uhi - ulo); e += 32) {
-                const int u = ulo + e;
-                const int j = (u + (rC + C)) / C - (a.r + 1), c = u - j * C;      // pixel offset (floor), channel
-                srow[u + a.O] = row[box_refl(x0p + j, a.w) * C + c];
+                             "l"(row + gx) : "memory");
+            } else {
+#pragma unroll
+                for (int kk = 0; kk < 4; ++kk) {
+                    const int uu = u + kk;
+                    if (uu < ulo || uu >= uhi) continue;
+                    const int j = (uu + (rC + C)) / C - (a.r + 1), c = uu - j * C;      // pixel offset (floor), channel
+                    srow[uu + a.O] = row[box_refl(x0p + j, a.w) * C + c];
+                }
             }
         }
     }
