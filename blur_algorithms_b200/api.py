@@ -150,6 +150,18 @@ class GaussPlan:
         check(lib.blur_b200_gauss_run_host(self._h, _ptr(h_in), _ptr(h_out)))
         return h_out
 
+    def run_host_batch(self, h_in: list, h_out: list | None = None):
+        """Stream a list of host images (numpy arrays or pinned CPU tensors) through the plan:
+        uploads, kernels and downloads of consecutive images overlap.  In place if h_out is None."""
+        h_out = h_in if h_out is None else h_out
+        if len(h_in) != len(h_out):
+            raise ValueError("h_in and h_out must have the same length")
+        n = len(h_in)
+        pin = (C.c_void_p * max(n, 1))(*[_ptr(a) for a in h_in])
+        pout = (C.c_void_p * max(n, 1))(*[_ptr(a) for a in h_out])
+        check(lib.blur_b200_gauss_run_host_batch(self._h, pin, pout, n))
+        return h_out
+
     def rowpass_f32(self, d_in, d_planar, stream: int | None = None):
         """float32 row-pass result as planar [3, rows, cols] (parity hook for `resf`, Source.cpp:536)."""
         check(lib.blur_b200_gauss_rowpass_f32(self._h, _ptr(d_in), _ptr(d_planar), _stream() if stream is None else stream))

@@ -112,13 +112,14 @@ __device__ __forceinline__ void il_octet(uint32_t b, uint32_t g, uint32_t r, uin
 
 __global__ void __launch_bounds__(256)
 interleave_oct_kernel(const uint8_t* __restrict__ u, uint8_t* __restrict__ out, int rows, int noct,
-                      int ncols /* valid columns to emit */, int out_cols /* row pitch of out, in pixels */, int vec)
+                      int ncols /* valid columns to emit */, int out_cols /* row pitch of out, in pixels */, int vec,
+                      int row_begin /* multiple of 4 */, int row_end)
 {
     const int op = blockIdx.x * 32 + threadIdx.x;          // octet pair
-    const int r0 = (blockIdx.y * 8 + threadIdx.y) * 4;     // first of 4 rows
+    const int r0 = row_begin + (blockIdx.y * 8 + threadIdx.y) * 4;     // first of 4 rows
     const int c0 = op * 16;
-    if (c0 >= ncols || r0 >= rows) return;
-    if (vec && c0 + 16 <= ncols && r0 + 4 <= rows) {
+    if (c0 >= ncols || r0 >= row_end) return;
+    if (vec && c0 + 16 <= ncols && r0 + 4 <= row_end) {
         uint4 v[3][2][2];                                   // [channel][octet][row pair]: x,y = row 2k, z,w = row 2k+1
 #pragma unroll
         for (int ch = 0; ch < 3; ++ch)
@@ -148,7 +149,7 @@ interleave_oct_kernel(const uint8_t* __restrict__ u, uint8_t* __restrict__ out, 
         return;
     }
     // ragged edge / unaligned pitch: byte by byte
-    for (int k = 0; k < 4 && r0 + k < rows; ++k)
+    for (int k = 0; k < 4 && r0 + k < row_end; ++k)
         for (int e = 0; e < 2 && 2 * op + e < noct; ++e)
             for (int px = 0; px < 8; ++px) {
                 const int c = c0 + 8 * e + px;
@@ -417,7 +418,14 @@ struct blur_b200_plan {
     int qpitch = 0, cpart = 0;        // overlap-save Q: floats per row / image columns per part
     float* d_q = nullptr;             // [nranks] blocks
     uint8_t* d_u = nullptr;           // [3][2*cpp][rows]
-    uint8_t* d_io = nullptr;          // staging for the host entry point (lazy)
+    // streamed host path (blur_b200_gauss_run_host_batch), all lazy: input / output images double
+    // buffered, one stream per PCIe direction, events (image parity x chunk)
+    uint8_t* d_sin[2] = {};
+    uint8_t* d_sout[2] = {};
+    cudaStream_t h2d_stream = nullptr, d2h_stream = nullptr;
+    static constexpr int kHostChunks = 8;
+    cudaEvent_t ev_h2d[kHostChunks] = {}, ev_out[kHostChunks + 1] = {};
+    cudaEvent_t ev_rowdone[2] = {}, ev_d2hdone[2] = {};
     float* d_q_recv = nullptr;        // unused on a single GPU
     int num_sms = 148;
     cudaStream_t stream = nullptr;
@@ -567,7 +575,8 @@ int run_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, float* d_q, cuda
     return BLUR_B200_OK;
 }
 
-int run_col_pass_to_u(blur_b200_plan* p, const float* d_q_chunks, cudaStream_t st)
+// blk_begin/blk_end: overlap-save blocks (of V output rows) to transform; blk_end < 0 = all
+int run_col_pass_to_u(blur_b200_plan* p, const float* d_q_chunks, cudaStream_t st, int blk_begin = 0, int blk_end = -1)
 {
     if (p->algo == 1) {
         OlsColIO io{};
@@ -575,7 +584,9 @@ int run_col_pass_to_u(blur_b200_plan* p, const float* d_q_chunks, cudaStream_t s
         io.rows = p->rows;
         io.noct = std::min(p->qpitch / 8, cdiv(std::max(0, p->cols - p->rank * p->cpart), 8));
         io.ax = p->ols_col;
-        io.nunits = io.ax.nblocks * 3 * io.noct;
+        if (blk_end < 0) blk_end = io.ax.nblocks;
+        io.b0 = blk_begin;
+        io.nunits = (blk_end - blk_begin) * 3 * io.noct;
         CU_TRY(launch_ols_col(io, d_q_chunks, p->qpitch, p->nranks * p->stripe_rows, p->d_ols_twa_col, p->d_ols_twb,
                               p->d_ols_kt_col, p->num_sms, st));
         ++g_launches;
@@ -596,15 +607,20 @@ int run_col_pass_to_u(blur_b200_plan* p, const float* d_q_chunks, cudaStream_t s
     return BLUR_B200_OK;
 }
 
-int run_interleave(blur_b200_plan* p, uint8_t* d_out, int ncols, int out_cols, cudaStream_t st)
+// row_begin (multiple of 4) / row_end: rows to emit, overlap-save plans only; row_end < 0 = all
+int run_interleave(blur_b200_plan* p, uint8_t* d_out, int ncols, int out_cols, cudaStream_t st, int row_begin = 0,
+                   int row_end = -1)
 {
     if (ncols <= 0) return BLUR_B200_OK;
+    if (row_end < 0) row_end = p->rows;
+    if (row_end <= row_begin) return BLUR_B200_OK;
     if (p->algo == 1) {
         const int noct = std::min(p->qpitch / 8, cdiv(std::max(0, p->cols - p->rank * p->cpart), 8));
         const int vec = (static_cast<size_t>(out_cols) * 3 % 16 == 0) && (reinterpret_cast<uintptr_t>(d_out) % 16 == 0) &&
                         (reinterpret_cast<uintptr_t>(p->d_u) % 32 == 0) && (p->rows % 4 == 0);
-        dim3 g(cdiv(cdiv(noct, 2), 32), cdiv(cdiv(p->rows, 4), 8));
-        interleave_oct_kernel<<<g, dim3(32, 8), 0, st>>>(p->d_u, d_out, p->rows, noct, std::min(ncols, noct * 8), out_cols, vec);
+        dim3 g(cdiv(cdiv(noct, 2), 32), cdiv(cdiv(row_end - row_begin, 4), 8));
+        interleave_oct_kernel<<<g, dim3(32, 8), 0, st>>>(p->d_u, d_out, p->rows, noct, std::min(ncols, noct * 8), out_cols, vec,
+                                                         row_begin, row_end);
         CU_TRY(cudaGetLastError());
         ++g_launches;
         return BLUR_B200_OK;
@@ -688,7 +704,15 @@ void blur_b200_gauss_plan_destroy(blur_b200_plan* p)
     cudaFree(p->col.d_tw); cudaFree(p->col.d_kt);
     cudaFree(p->d_ols_twa_row); cudaFree(p->d_ols_twa_col); cudaFree(p->d_ols_twb);
     cudaFree(p->d_ols_kt_row); cudaFree(p->d_ols_kt_col);
-    cudaFree(p->d_q); cudaFree(p->d_u); cudaFree(p->d_io);
+    cudaFree(p->d_q); cudaFree(p->d_u);
+    for (uint8_t* b : p->d_sin) cudaFree(b);
+    for (uint8_t* b : p->d_sout) cudaFree(b);
+    if (p->h2d_stream) cudaStreamDestroy(p->h2d_stream);
+    if (p->d2h_stream) cudaStreamDestroy(p->d2h_stream);
+    for (cudaEvent_t e : p->ev_h2d) if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : p->ev_out) if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : p->ev_rowdone) if (e) cudaEventDestroy(e);
+    for (cudaEvent_t e : p->ev_d2hdone) if (e) cudaEventDestroy(e);
     if (p->stream) cudaStreamDestroy(p->stream);
     if (p->push_stream) cudaStreamDestroy(p->push_stream);
     for (cudaEvent_t e : p->ev_chunk) if (e) cudaEventDestroy(e);
@@ -731,18 +755,99 @@ int blur_b200_gauss_run_device(blur_b200_plan* p, const uint8_t* d_in, uint8_t* 
     return run_interleave(p, d_out, p->cols, p->cols, st);
 }
 
+// Streamed host path: n host images through one plan.  Three streams — H2D, compute,
+// D2H — and double-buffered device images: the upload of image i+1 and the download of image
+// i-1 run underneath the kernels of image i, and inside one image the row pass starts on the
+// first chunk of rows as soon as it has arrived while the column pass hands finished overlap-save
+// blocks (V rows, all columns) to the download stream.  PCIe is full duplex, so the steady state
+// costs one image transfer per direction per image instead of upload + blur + download.
+int blur_b200_gauss_run_host_batch(blur_b200_plan* p, const uint8_t* const* h_in, uint8_t* const* h_out, int n)
+{
+    if (!p || !h_in || !h_out || n < 0 || p->nranks != 1) return BLUR_B200_EINVAL;
+    for (int i = 0; i < n; ++i)
+        if (!h_in[i] || !h_out[i]) return BLUR_B200_EINVAL;
+    if (n == 0) return BLUR_B200_OK;
+    CU_TRY(cudaSetDevice(p->device));
+    const size_t pitch = static_cast<size_t>(p->cols) * 3;
+    const size_t nbytes = pitch * p->rows;
+    const int nbuf = n > 1 ? 2 : 1;
+    if (!p->h2d_stream) {
+        CU_TRY(cudaStreamCreateWithFlags(&p->h2d_stream, cudaStreamNonBlocking));
+        CU_TRY(cudaStreamCreateWithFlags(&p->d2h_stream, cudaStreamNonBlocking));
+        for (cudaEvent_t& e : p->ev_h2d) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        for (cudaEvent_t& e : p->ev_out) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        for (cudaEvent_t& e : p->ev_rowdone) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        for (cudaEvent_t& e : p->ev_d2hdone) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    }
+    for (int k = 0; k < nbuf; ++k) {
+        if (!p->d_sin[k]) CU_TRY(cudaMalloc(&p->d_sin[k], nbytes));
+        if (!p->d_sout[k]) CU_TRY(cudaMalloc(&p->d_sout[k], nbytes));
+    }
+    cudaStream_t sc = p->stream;
+    const bool ols = p->algo == 1;
+    // row chunks: whole waves of the persistent row grid (see blur_b200_gauss_row_pass_push)
+    const int npairs = cdiv(p->rows, 2);
+    int nchunks = 1, wave_pairs = npairs, nwaves = 1;
+    if (ols) {
+        wave_pairs = std::max(1, p->num_sms * ols_resident_ctas(p->ols_row.R0) / std::max(1, p->ols_row.nblocks));
+        nwaves = cdiv(npairs, wave_pairs);
+        nchunks = std::max(1, std::min<int>(blur_b200_plan::kHostChunks, nwaves / 2));
+    }
+    const int nblk = ols ? std::min<int>(p->ols_col.nblocks, blur_b200_plan::kHostChunks) : 1;
+    for (int i = 0; i < n; ++i) {
+        const int k = i & (nbuf - 1);
+        if (i >= nbuf) CU_TRY(cudaStreamWaitEvent(p->h2d_stream, p->ev_rowdone[k], 0));     // row pass of image i-2 has read d_sin[k]
+        for (int c = 0; c < nchunks; ++c) {
+            const int p0 = std::min(npairs, static_cast<int>(static_cast<int64_t>(nwaves) * c / nchunks) * wave_pairs);
+            const int p1 = c + 1 == nchunks ? npairs : std::min(npairs, static_cast<int>(static_cast<int64_t>(nwaves) * (c + 1) / nchunks) * wave_pairs);
+            const int r0 = 2 * p0, r1 = std::min(2 * p1, p->rows);
+            if (r1 <= r0) continue;
+            CU_TRY(cudaMemcpyAsync(p->d_sin[k] + r0 * pitch, h_in[i] + r0 * pitch, (r1 - r0) * pitch, cudaMemcpyHostToDevice, p->h2d_stream));
+            CU_TRY(cudaEventRecord(p->ev_h2d[c], p->h2d_stream));
+            CU_TRY(cudaStreamWaitEvent(sc, p->ev_h2d[c], 0));
+            if (ols) {
+                OlsRowIO io{};
+                io.in = p->d_sin[k] + r0 * pitch;
+                io.q = p->d_q + static_cast<size_t>(r0) * p->qpitch;
+                io.rows = r1 - r0; io.cols = p->cols;
+                io.npairs = cdiv(io.rows, 2);
+                io.srows = p->stripe_rows; io.qpitch = p->qpitch; io.cpart = p->cpart; io.nparts = 1;
+                io.ax = p->ols_row;
+                io.nunits = io.ax.nblocks * io.npairs;
+                CU_TRY(launch_ols_row(io, p->d_ols_twa_row, p->d_ols_twb, p->d_ols_kt_row, p->num_sms, sc));
+                ++g_launches;
+            } else {
+                const int rc = run_row_pass(p, p->d_sin[k], p->d_q, sc);
+                if (rc) return rc;
+            }
+        }
+        CU_TRY(cudaEventRecord(p->ev_rowdone[k], sc));
+        if (i >= nbuf) CU_TRY(cudaStreamWaitEvent(sc, p->ev_d2hdone[k], 0));                 // image i-2 has left d_sout[k]
+        int rows_out = 0;
+        for (int b = 0; b < nblk; ++b) {
+            const bool last = b + 1 == nblk;
+            int rc = run_col_pass_to_u(p, p->d_q, sc, ols ? b : 0, ols ? (last ? p->ols_col.nblocks : b + 1) : -1);
+            if (rc) return rc;
+            const int rend = last ? p->rows : std::min(p->rows, (b + 1) * p->ols_col.V) & ~3;
+            if (rend <= rows_out) continue;
+            rc = run_interleave(p, p->d_sout[k], p->cols, p->cols, sc, rows_out, rend);
+            if (rc) return rc;
+            CU_TRY(cudaEventRecord(p->ev_out[b], sc));
+            CU_TRY(cudaStreamWaitEvent(p->d2h_stream, p->ev_out[b], 0));
+            CU_TRY(cudaMemcpyAsync(h_out[i] + rows_out * pitch, p->d_sout[k] + rows_out * pitch, (rend - rows_out) * pitch,
+                                   cudaMemcpyDeviceToHost, p->d2h_stream));
+            rows_out = rend;
+        }
+        CU_TRY(cudaEventRecord(p->ev_d2hdone[k], p->d2h_stream));
+    }
+    CU_TRY(cudaStreamSynchronize(p->d2h_stream));
+    CU_TRY(cudaStreamSynchronize(sc));
+    return BLUR_B200_OK;
+}
+
 int blur_b200_gauss_run_host(blur_b200_plan* p, const uint8_t* h_in, uint8_t* h_out)
 {
-    if (!p || !h_in || !h_out || p->nranks != 1) return BLUR_B200_EINVAL;
-    CU_TRY(cudaSetDevice(p->device));
-    const size_t nbytes = static_cast<size_t>(p->rows) * p->cols * 3;
-    if (!p->d_io) CU_TRY(cudaMalloc(&p->d_io, nbytes));
-    CU_TRY(cudaMemcpyAsync(p->d_io, h_in, nbytes, cudaMemcpyHostToDevice, p->stream));
-    int rc = blur_b200_gauss_run_device(p, p->d_io, p->d_io, p->stream);
-    if (rc) return rc;
-    CU_TRY(cudaMemcpyAsync(h_out, p->d_io, nbytes, cudaMemcpyDeviceToHost, p->stream));
-    CU_TRY(cudaStreamSynchronize(p->stream));
-    return BLUR_B200_OK;
+    return blur_b200_gauss_run_host_batch(p, &h_in, &h_out, 1);
 }
 
 int blur_b200_gauss_u8c3(uint8_t* h_bgr, int rows, int cols, double sigma, int nyquist_mode)

@@ -399,6 +399,7 @@ struct OlsColIO {
     int noct;              // column octets handled here
     int nunits;
     OlsAxis ax;            // len = rows
+    int b0;                // first block of this launch (the streamed host path launches block by block)
 
     struct Ctx {
         uint8_t* ua;       // U byte of (ch, oct, row 0, 0)
@@ -414,7 +415,7 @@ struct OlsColIO {
         c.oct = unit % noct;
         const int rest = unit / noct;
         c.ch = rest % 3;
-        const int b = rest / 3;
+        const int b = b0 + rest / 3;
         c.ua = u + (static_cast<size_t>(c.ch) * noct + c.oct) * rows * 8;
         c.qa = q + static_cast<size_t>(c.ch) * rows_total * qpitch + c.oct * 8;
         c.s = b * ax.V - ax.halo;

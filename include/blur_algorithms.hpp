@@ -39,6 +39,9 @@ public:
     GaussPlan& operator=(const GaussPlan&) = delete;
     // host buffers, in place allowed (image.data)
     void run(const uint8_t* h_in, uint8_t* h_out) { check(blur_b200_gauss_run_host(p_, h_in, h_out), "gauss_run_host"); }
+    // n host images streamed through the plan (uploads, kernels and downloads overlap)
+    void run_batch(const uint8_t* const* h_in, uint8_t* const* h_out, int n)
+    { check(blur_b200_gauss_run_host_batch(p_, h_in, h_out, n), "gauss_run_host_batch"); }
     // device buffers on the plan's device, in place allowed; stream = cudaStream_t
     void run_device(const uint8_t* d_in, uint8_t* d_out, void* stream = nullptr)
     { check(blur_b200_gauss_run_device(p_, d_in, d_out, stream), "gauss_run_device"); }

@@ -100,6 +100,15 @@ int blur_b200_gauss_run_device(blur_b200_plan *plan, const uint8_t *d_in, uint8_
 /* Whole blur on host buffers (pinned or pageable); H2D + kernels + D2H.  In place allowed. */
 int blur_b200_gauss_run_host(blur_b200_plan *plan, const uint8_t *h_in, uint8_t *h_out);
 
+/* Streamed host path (the reference's `Test` loop over images, Source.cpp:574-608,
+ * 625-634, blurs one host image per call): n host images of the plan's size through one plan.
+ * Upload of image i+1, kernels of image i and download of image i-1 overlap (three streams,
+ * double-buffered device images); inside one image the row pass follows the upload chunk by chunk
+ * and finished row blocks of the column pass are downloaded while the next block is transformed.
+ * Pinned host buffers are needed for the overlap (pageable ones still work).  h_out[i] may equal
+ * h_in[i].  blur_b200_gauss_run_host is this call with n = 1. */
+int blur_b200_gauss_run_host_batch(blur_b200_plan *plan, const uint8_t *const *h_in, uint8_t *const *h_out, int n);
+
 /* One-shot drop-in for `pffft_(image, sigma)` / `pocketfft_1D` / `pocketfft_2D` acting on
  * image.data in place (Source.cpp:429,280,143): creates a plan, runs, destroys. */
 int blur_b200_gauss_u8c3(uint8_t *h_bgr, int rows, int cols, double sigma, int nyquist_mode);

@@ -105,6 +105,32 @@ def test_gauss_device_entry_in_place_and_repeatable(bb, oracle, torch):
     plan.close()
 
 
+@pytest.mark.parametrize("rows,cols,sigma", [(300, 200, 4.0), (1536, 1100, 9.0), (6001, 517, 3.0)])
+def test_gauss_host_batch_streamed(bb, torch, rows, cols, sigma):
+    """blur_b200_gauss_run_host_batch: n images through the three-stream pipeline (chunked upload /
+    row pass, blockwise column pass / download, double-buffered images) == the device entry."""
+    plan = bb.GaussPlan(rows, cols, sigma, 0)
+    imgs = [synth("noise", rows, cols, 20 + i) for i in range(5)]
+    want = []
+    for im in imgs:
+        d = torch.from_numpy(im).cuda()
+        plan.run(d)
+        torch.cuda.synchronize()
+        want.append(d.cpu().numpy())
+    pinned_in = [torch.from_numpy(im.copy()).pin_memory() for im in imgs]
+    pinned_out = [torch.empty_like(t).pin_memory() for t in pinned_in]
+    plan.run_host_batch([t.numpy() for t in pinned_in], [t.numpy() for t in pinned_out])
+    for w, o in zip(want, pinned_out):
+        assert np.array_equal(w, o.numpy())
+    # in place, pageable memory, odd count
+    hs = [im.copy() for im in imgs[:3]]
+    plan.run_host_batch(hs)
+    for w, h in zip(want, hs):
+        assert np.array_equal(w, h)
+    plan.run_host_batch([])
+    plan.close()
+
+
 def test_gauss_errors(bb):
     with pytest.raises(bb.BlurB200Error) as e:
         bb.pffft_(synth("noise", 16, 400), 50.0)      # pad 165 > rows-1: reference would read OOB
