@@ -12,6 +12,7 @@
 #include <cuda_runtime.h>
 
 #include <algorithm>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -144,30 +145,34 @@ spec_rows_kernel(const __grid_constant__ FftGeom g, const __grid_constant__ Rows
     // B[k] = (Z[k] - conj Z[N-k]) / (2i)
     const int H2 = io.H / 2, WC = N / 2 + 1;
     const int ch = unit / H2, rp = unit - ch * H2;
-    float2* ga = G + (static_cast<size_t>(ch) * io.H + 2 * rp) * WC;
-    float2* gb = ga + WC;
+    // G is tiled by column quads: element (ch, row, k) lives at ((ch*NG + k/4)*H + row)*4 + k%4, so
+    // four consecutive k of a row are one 32-byte sector here and one sector per row in the column
+    // kernel (a plain [row][k] layout costs the column pass a whole sector per 8-byte element)
+    const int NG = (WC + 3) >> 2;
+    float2* ga = G + (static_cast<size_t>(ch) * NG * io.H + 2 * rp) * 4;
     for (int k = tid; k < WC; k += T) {
         const int nk = k ? N - k : 0;
         const float2 z = smem[k + (k >> 5)], c = smem[nk + (nk >> 5)];
-        ga[k] = make_float2(0.5f * (z.x + c.x), 0.5f * (z.y - c.y));
-        gb[k] = make_float2(0.5f * (z.y + c.y), -0.5f * (z.x - c.x));
+        float2* d = ga + static_cast<size_t>(k >> 2) * io.H * 4 + (k & 3);
+        d[0] = make_float2(0.5f * (z.x + c.x), 0.5f * (z.y - c.y));
+        d[4] = make_float2(0.5f * (z.y + c.y), -0.5f * (z.x - c.x));
     }
 }
 
 struct ColsIO {
-    const float2* G;   // [3][H][WC]
+    const float2* G;   // [3][NG][H][4], NG = ceil(WC / 4) column quads
     int H, WC;
     struct Ctx { const float2* p; };
     __device__ __forceinline__ Ctx begin(int unit) const
     {
         const int ch = unit / WC, k = unit - ch * WC;
         Ctx c;
-        c.p = G + static_cast<size_t>(ch) * H * WC + k;
+        c.p = G + (static_cast<size_t>(ch) * ((WC + 3) >> 2) + (k >> 2)) * H * 4 + (k & 3);
         return c;
     }
     __device__ __forceinline__ void load(const Ctx& c, int n, float& re, float& im) const
     {
-        const float2 v = c.p[static_cast<size_t>(n) * WC];
+        const float2 v = c.p[static_cast<size_t>(n) * 4];
         re = v.x; im = v.y;
     }
     __device__ __forceinline__ void store(const Ctx&, int, float, float) const {}
@@ -248,6 +253,16 @@ thread_local std::string g_err;
         }                                                                        \
     } while (0)
 
+// Twiddles and the half-spectrum workspace G are kept between calls (one geometry per device at a
+// time): the reference re-plans on every call (pocketfft's plan cache aside), here a repeated
+// call costs two kernel launches.
+struct SpecWs {
+    int device = -1, H = 0, W = 0;
+    float2 *tww = nullptr, *twh = nullptr, *G = nullptr;
+};
+std::mutex g_ws_mutex;
+SpecWs g_ws;
+
 int threads_for(int n32) { return std::max(128, std::min(kMaxThreads, ((n32 + 31) / 32) * 32)); }
 
 }  // namespace
@@ -278,18 +293,27 @@ int blur_b200_dft_image_device(const uint8_t* d_in, uint8_t* d_out, int rows, in
     // the un-scramble step keeps one radix-32 group per thread in registers
     if (gm.W / 32 > kMaxThreads || gm.H / 32 > kMaxThreads) return BLUR_B200_ESIZE;
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    std::vector<float2> tw;
-    float2 *d_tww = nullptr, *d_twh = nullptr, *d_G = nullptr;
-    make_twiddles(gm.W, tw);
-    CU_TRY(cudaMalloc(&d_tww, sizeof(float2) * tw.size()));
-    CU_TRY(cudaMemcpyAsync(d_tww, tw.data(), sizeof(float2) * tw.size(), cudaMemcpyHostToDevice, st));
-    CU_TRY(cudaStreamSynchronize(st));
-    make_twiddles(gm.H, tw);
-    CU_TRY(cudaMalloc(&d_twh, sizeof(float2) * tw.size()));
-    CU_TRY(cudaMemcpyAsync(d_twh, tw.data(), sizeof(float2) * tw.size(), cudaMemcpyHostToDevice, st));
-    CU_TRY(cudaStreamSynchronize(st));
+    std::lock_guard<std::mutex> lock(g_ws_mutex);
+    int device = 0;
+    CU_TRY(cudaGetDevice(&device));
     const int WC = gm.W / 2 + 1;
-    CU_TRY(cudaMalloc(&d_G, sizeof(float2) * static_cast<size_t>(3) * gm.H * WC));
+    if (g_ws.device != device || g_ws.H != gm.H || g_ws.W != gm.W) {
+        if (g_ws.device >= 0) {
+            CU_TRY(cudaDeviceSynchronize());
+            cudaFree(g_ws.tww); cudaFree(g_ws.twh); cudaFree(g_ws.G);
+            g_ws = SpecWs();
+        }
+        std::vector<float2> tw;
+        make_twiddles(gm.W, tw);
+        CU_TRY(cudaMalloc(&g_ws.tww, sizeof(float2) * tw.size()));
+        CU_TRY(cudaMemcpy(g_ws.tww, tw.data(), sizeof(float2) * tw.size(), cudaMemcpyHostToDevice));
+        make_twiddles(gm.H, tw);
+        CU_TRY(cudaMalloc(&g_ws.twh, sizeof(float2) * tw.size()));
+        CU_TRY(cudaMemcpy(g_ws.twh, tw.data(), sizeof(float2) * tw.size(), cudaMemcpyHostToDevice));
+        CU_TRY(cudaMalloc(&g_ws.G, sizeof(float2) * static_cast<size_t>(3) * ((WC + 3) / 4) * 4 * gm.H));
+        g_ws.device = device; g_ws.H = gm.H; g_ws.W = gm.W;
+    }
+    float2 *d_tww = g_ws.tww, *d_twh = g_ws.twh, *d_G = g_ws.G;
 
     const size_t smem_w = static_cast<size_t>(gw.slots) * 8, smem_h = static_cast<size_t>(gh.slots) * 8;
     CU_TRY(cudaFuncSetAttribute(spec_rows_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_w)));
@@ -302,8 +326,7 @@ int blur_b200_dft_image_device(const uint8_t* d_in, uint8_t* d_out, int rows, in
                                                                      gm.border[0], gm.border[2]);
     CU_TRY(cudaGetLastError());
     blur_b200_count_launches(2);
-    CU_TRY(cudaStreamSynchronize(st));
-    cudaFree(d_tww); cudaFree(d_twh); cudaFree(d_G);
+    CU_TRY(cudaStreamSynchronize(st));      // the shared workspace is free again when the call returns
     return BLUR_B200_OK;
 }
 
