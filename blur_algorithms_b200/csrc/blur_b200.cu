@@ -228,6 +228,112 @@ __global__ void transpose_f32_kernel(const float* __restrict__ in, float* __rest
     }
 }
 
+// ---- pffft Nyquist quirk on the overlap-save path (Source.cpp:414-427) -----------
+// The reference's pffft_ result per line is  exact[x] + c * (-1)^x * A,  c = (K[0] - K[N/2]) / N,
+// A = sum over the reflect-padded tile of tile[m] (-1)^m = sum_x w_x (-1)^x line[x] (the pad parity
+// cancels), w_x = 1 + [1 <= x <= pad] + [len-1-pad <= x <= len-2].  These two kernels produce c * A
+// per line; the FFT kernels add it in their epilogues.
+__device__ __forceinline__ int quirk_weight(int x, int len, int pad)
+{
+    return 1 + ((x >= 1 && x <= pad) ? 1 : 0) + ((x >= len - 1 - pad && x <= len - 2) ? 1 : 0);
+}
+
+// unsigned bytes of a  x  signed bytes of b, accumulated
+__device__ __forceinline__ int dp4a_us(uint32_t a, int b, int acc)
+{
+    int r;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(acc));
+    return r;
+}
+
+// rows: exact integer sums over the uint8 line.  grid = rows, 128 threads.  corr[ch * pitch + row].
+// vec: cols % 4 == 0 and a 4-byte aligned image -> a thread takes 4 pixels as three 32-bit words
+// and weights them with dp4a (signed selector bytes = weight * sign of each pixel).
+__global__ void __launch_bounds__(128)
+quirk_rows_kernel(const uint8_t* __restrict__ in, int cols, int pad, double c, float* __restrict__ corr, int pitch, int vec)
+{
+    __shared__ int part[4][3];
+    const int row = blockIdx.x, tid = threadIdx.x;
+    const uint8_t* line = in + static_cast<size_t>(row) * cols * 3;
+    int acc[3] = {0, 0, 0};
+    if (vec) {
+        const uint32_t* lw = reinterpret_cast<const uint32_t*>(line);
+        for (int g = tid; g < cols / 4; g += 128) {
+            const uint32_t w0 = __ldg(lw + 3 * g), w1 = __ldg(lw + 3 * g + 1), w2 = __ldg(lw + 3 * g + 2);
+            const int x = 4 * g;
+            const uint32_t s0 = static_cast<uint8_t>(quirk_weight(x, cols, pad)), s1 = static_cast<uint8_t>(-quirk_weight(x + 1, cols, pad)),
+                           s2 = static_cast<uint8_t>(quirk_weight(x + 2, cols, pad)), s3 = static_cast<uint8_t>(-quirk_weight(x + 3, cols, pad));
+            // bytes: w0 = B0 G0 R0 B1, w1 = G1 R1 B2 G2, w2 = R2 B3 G3 R3
+            acc[0] = dp4a_us(w0, static_cast<int>(s0 | (s1 << 24)), acc[0]);
+            acc[0] = dp4a_us(w1, static_cast<int>(s2 << 16), acc[0]);
+            acc[0] = dp4a_us(w2, static_cast<int>(s3 << 8), acc[0]);
+            acc[1] = dp4a_us(w0, static_cast<int>(s0 << 8), acc[1]);
+            acc[1] = dp4a_us(w1, static_cast<int>(s1 | (s2 << 24)), acc[1]);
+            acc[1] = dp4a_us(w2, static_cast<int>(s3 << 16), acc[1]);
+            acc[2] = dp4a_us(w0, static_cast<int>(s0 << 16), acc[2]);
+            acc[2] = dp4a_us(w1, static_cast<int>(s1 << 8), acc[2]);
+            acc[2] = dp4a_us(w2, static_cast<int>(s2 | (s3 << 24)), acc[2]);
+        }
+    } else {
+        for (int x = tid; x < cols; x += 128) {
+            const int w = quirk_weight(x, cols, pad) * ((x & 1) ? -1 : 1);
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch) acc[ch] += w * line[3 * x + ch];
+        }
+    }
+#pragma unroll
+    for (int ch = 0; ch < 3; ++ch) {
+        int v = acc[ch];
+        for (int d = 16; d; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+        if ((tid & 31) == 0) part[tid >> 5][ch] = v;
+    }
+    __syncthreads();
+    if (tid < 3) corr[static_cast<size_t>(tid) * pitch + row] =
+        static_cast<float>(c * static_cast<double>(part[0][tid] + part[1][tid] + part[2][tid] + part[3][tid]));
+}
+
+// columns of Q [3][srows][qpitch] (single GPU), two steps with a fixed summation order:
+// quirk_cols_partial: block (32 column quads, 8 row lanes), grid (ceil(qpitch/128), 3, kQuirkSeg row
+// segments), float4 loads, double accumulators -> part[seg][ch][col];  quirk_cols_final: corr = c * sum.
+constexpr int kQuirkSeg = 8;
+__global__ void __launch_bounds__(256)
+quirk_cols_partial(const float* __restrict__ q, int rows, int srows, int qpitch, int pad, double* __restrict__ partial)
+{
+    __shared__ double sm[8][32][4];
+    const int col = (blockIdx.x * 32 + threadIdx.x) * 4, ch = blockIdx.y, ry = threadIdx.y;
+    const int seg_rows = (rows + kQuirkSeg - 1) / kQuirkSeg;
+    const int r_begin = blockIdx.z * seg_rows, r_end = min(rows, r_begin + seg_rows);
+    double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+    if (col < qpitch) {
+        const float* p = q + static_cast<size_t>(ch) * srows * qpitch + col;
+#pragma unroll 4
+        for (int r = r_begin + ry; r < r_end; r += 8) {
+            const float4 v = __ldg(reinterpret_cast<const float4*>(p + static_cast<size_t>(r) * qpitch));
+            const double w = quirk_weight(r, rows, pad) * ((r & 1) ? -1 : 1);
+            a0 += w * v.x; a1 += w * v.y; a2 += w * v.z; a3 += w * v.w;
+        }
+    }
+    sm[ry][threadIdx.x][0] = a0; sm[ry][threadIdx.x][1] = a1; sm[ry][threadIdx.x][2] = a2; sm[ry][threadIdx.x][3] = a3;
+    __syncthreads();
+    const int t = ry * 32 + threadIdx.x;           // 128 columns of this block
+    if (t < 128 && blockIdx.x * 128 + t < qpitch) {
+        double s = 0;
+#pragma unroll
+        for (int k = 0; k < 8; ++k) s += sm[k][t >> 2][t & 3];
+        partial[(static_cast<size_t>(blockIdx.z) * 3 + ch) * qpitch + blockIdx.x * 128 + t] = s;
+    }
+}
+
+__global__ void quirk_cols_final(const double* __restrict__ partial, int n /* 3 * qpitch */, double c, float* __restrict__ corr)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    double s = 0;
+#pragma unroll
+    for (int k = 0; k < kQuirkSeg; ++k) s += partial[static_cast<size_t>(k) * n + i];
+    corr[i] = static_cast<float>(c * s);
+}
+
 // ------------------------------------------------------------------ exchange kernel
 // The distributed flip_block (Source.cpp:540) of the sharded plan: after a chunk of row pairs has
 // been transformed into the local send buffer, this kernel pushes the blocks owned by the other
@@ -418,6 +524,11 @@ struct blur_b200_plan {
     int qpitch = 0, cpart = 0;        // overlap-save Q: floats per row / image columns per part
     float* d_q = nullptr;             // [nranks] blocks
     uint8_t* d_u = nullptr;           // [3][2*cpp][rows]
+    // pffft Nyquist quirk served by the overlap-save kernels (single GPU): per-line corrections
+    bool quirk_ols = false;
+    double quirk_c_row = 0, quirk_c_col = 0;      // (K[0] - K[N/2]) / N of each axis
+    float *d_corr_row = nullptr, *d_corr_col = nullptr;   // [3][rows], [3][qpitch]
+    double* d_corr_part = nullptr;                        // [kQuirkSeg][3][qpitch]
     // streamed host path (blur_b200_gauss_run_host_batch), all lazy: input / output images double
     // buffered, one stream per PCIe direction, events (image parity x chunk)
     uint8_t* d_sin[2] = {};
@@ -528,6 +639,24 @@ int plan_create(blur_b200_plan** out, int rows, int cols, double sigma, int mode
     int rc = BLUR_B200_OK;
     if (p->algo == 1) {
         rc = build_ols_tables(p, sigma, gg.ksize);
+        if (rc == BLUR_B200_OK && mode == 1) {
+            // K[0] = sum of the taps, K[N/2] = alternating sum (the taps are symmetric about index 0)
+            std::vector<float> taps;
+            for (int axis = 0; axis < 2; ++axis) {
+                const int N = axis ? gg.n_col : gg.n_row;
+                get_gaussian(taps, sigma, gg.ksize, N);
+                double k0 = 0, kn = 0;
+                for (int n = 0; n < N; ++n) { k0 += taps[n]; kn += (n & 1) ? -static_cast<double>(taps[n]) : taps[n]; }
+                // float products like the reference: kernel_dft[0] * scaler (Source.cpp:423,506-507)
+                const float scaler = 1.f / static_cast<float>(N);
+                (axis ? p->quirk_c_col : p->quirk_c_row) =
+                    static_cast<double>(static_cast<float>(k0) * scaler) - static_cast<double>(static_cast<float>(kn) * scaler);
+            }
+            p->quirk_ols = true;
+            CU_TRY(cudaMalloc(&p->d_corr_row, sizeof(float) * 3 * rows));
+            CU_TRY(cudaMalloc(&p->d_corr_col, sizeof(float) * 3 * p->qpitch));
+            CU_TRY(cudaMalloc(&p->d_corr_part, sizeof(double) * 8 * 3 * p->qpitch));
+        }
     } else {
         rc = build_axis(p->row, gg.n_row, sigma, gg.ksize, mode);
         if (rc == BLUR_B200_OK) rc = build_axis(p->col, gg.n_col, sigma, gg.ksize, mode);
@@ -555,6 +684,13 @@ int run_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, float* d_q, cuda
         io.srows = p->stripe_rows; io.qpitch = p->qpitch; io.cpart = p->cpart; io.nparts = p->nranks;
         io.ax = p->ols_row;
         io.nunits = io.ax.nblocks * io.npairs;
+        if (p->quirk_ols) {
+            quirk_rows_kernel<<<p->valid_rows, 128, 0, st>>>(d_in_stripe, p->cols, p->gg.pad, p->quirk_c_row, p->d_corr_row, p->rows,
+                                                             p->cols % 4 == 0 && reinterpret_cast<uintptr_t>(d_in_stripe) % 4 == 0);
+            CU_TRY(cudaGetLastError());
+            ++g_launches;
+            io.corr = p->d_corr_row; io.corr_pitch = p->rows;
+        }
         if (peers && p->nranks > 1) {
             io.peer = 1; io.rank = p->rank;
             for (int k = 0; k < p->nranks; ++k) io.qpeer[k] = peers[k];
@@ -587,6 +723,17 @@ int run_col_pass_to_u(blur_b200_plan* p, const float* d_q_chunks, cudaStream_t s
         if (blk_end < 0) blk_end = io.ax.nblocks;
         io.b0 = blk_begin;
         io.nunits = (blk_end - blk_begin) * 3 * io.noct;
+        if (p->quirk_ols) {
+            if (blk_begin == 0) {
+                quirk_cols_partial<<<dim3(cdiv(p->qpitch, 128), 3, kQuirkSeg), dim3(32, 8), 0, st>>>(d_q_chunks, p->rows, p->stripe_rows,
+                                                                                                 p->qpitch, p->gg.pad, p->d_corr_part);
+                CU_TRY(cudaGetLastError());
+                quirk_cols_final<<<cdiv(3 * p->qpitch, 256), 256, 0, st>>>(p->d_corr_part, 3 * p->qpitch, p->quirk_c_col, p->d_corr_col);
+                CU_TRY(cudaGetLastError());
+                g_launches += 2;
+            }
+            io.corr = p->d_corr_col; io.corr_pitch = p->qpitch;
+        }
         CU_TRY(launch_ols_col(io, d_q_chunks, p->qpitch, p->nranks * p->stripe_rows, p->d_ols_twa_col, p->d_ols_twb,
                               p->d_ols_kt_col, p->num_sms, st));
         ++g_launches;
@@ -704,7 +851,7 @@ void blur_b200_gauss_plan_destroy(blur_b200_plan* p)
     cudaFree(p->col.d_tw); cudaFree(p->col.d_kt);
     cudaFree(p->d_ols_twa_row); cudaFree(p->d_ols_twa_col); cudaFree(p->d_ols_twb);
     cudaFree(p->d_ols_kt_row); cudaFree(p->d_ols_kt_col);
-    cudaFree(p->d_q); cudaFree(p->d_u);
+    cudaFree(p->d_q); cudaFree(p->d_u); cudaFree(p->d_corr_row); cudaFree(p->d_corr_col); cudaFree(p->d_corr_part);
     for (uint8_t* b : p->d_sin) cudaFree(b);
     for (uint8_t* b : p->d_sout) cudaFree(b);
     if (p->h2d_stream) cudaStreamDestroy(p->h2d_stream);
@@ -814,6 +961,13 @@ int blur_b200_gauss_run_host_batch(blur_b200_plan* p, const uint8_t* const* h_in
                 io.srows = p->stripe_rows; io.qpitch = p->qpitch; io.cpart = p->cpart; io.nparts = 1;
                 io.ax = p->ols_row;
                 io.nunits = io.ax.nblocks * io.npairs;
+                if (p->quirk_ols) {
+                    quirk_rows_kernel<<<io.rows, 128, 0, sc>>>(io.in, p->cols, p->gg.pad, p->quirk_c_row, p->d_corr_row + r0, p->rows,
+                                                               p->cols % 4 == 0 && reinterpret_cast<uintptr_t>(io.in) % 4 == 0);
+                    CU_TRY(cudaGetLastError());
+                    ++g_launches;
+                    io.corr = p->d_corr_row + r0; io.corr_pitch = p->rows;
+                }
                 CU_TRY(launch_ols_row(io, p->d_ols_twa_row, p->d_ols_twb, p->d_ols_kt_row, p->num_sms, sc));
                 ++g_launches;
             } else {
@@ -871,7 +1025,7 @@ int blur_b200_gauss_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, floa
 int blur_b200_gauss_row_pass_peer(blur_b200_plan* p, const uint8_t* d_in_stripe, float* const* q_peers, int npeers, void* stream)
 {
     if (!p || !d_in_stripe || !q_peers || npeers != p->nranks || npeers > OlsRowIO::kMaxPeers) return BLUR_B200_EINVAL;
-    if (p->algo != 1) return BLUR_B200_ESIZE;      // only the overlap-save row kernel has the fused epilogue
+    if (p->algo != 1 || p->quirk_ols) return BLUR_B200_ESIZE;      // only the overlap-save row kernel has the fused epilogue
     for (int k = 0; k < npeers; ++k)
         if (!q_peers[k]) return BLUR_B200_EINVAL;
     return run_row_pass(p, d_in_stripe, p->d_q, static_cast<cudaStream_t>(stream), q_peers);
@@ -881,7 +1035,7 @@ int blur_b200_gauss_row_pass_push(blur_b200_plan* p, const uint8_t* d_in_stripe,
                                   int nchunks, void* stream)
 {
     if (!p || !d_in_stripe || !q_peers || npeers != p->nranks || npeers > OlsRowIO::kMaxPeers) return BLUR_B200_EINVAL;
-    if (p->algo != 1) return BLUR_B200_ESIZE;
+    if (p->algo != 1 || p->quirk_ols) return BLUR_B200_ESIZE;
     for (int k = 0; k < npeers; ++k)
         if (!q_peers[k]) return BLUR_B200_EINVAL;
     if (p->valid_rows <= 0) return BLUR_B200_OK;

@@ -228,6 +228,11 @@ struct OlsRowIO {
     static constexpr int kMaxPeers = 8;
     float* qpeer[kMaxPeers];
     int rank, peer;
+    // pffft Nyquist quirk (Source.cpp:414-427) on top of the exact blocks: the reference's result is
+    // exact + c * (-1)^x * A with A = alternating sum of the reflect-padded line;
+    // corr[ch * corr_pitch + line] = c * A, added in the epilogue.  nullptr = exact mode.
+    const float* corr;
+    int corr_pitch;
 
     struct Stage {
         const uint8_t* src;  // 16-byte aligned global address of the first vector
@@ -322,8 +327,18 @@ struct OlsRowIO {
         }
     }
     template <int R0>
-    BLUR_HD void store_item(const Ctx& c, int X, int t, const cplx (&x)[R0]) const
+    BLUR_HD void store_item(const Ctx& c, int X, int t, const cplx (&xin)[R0]) const
     {
+        cplx x[R0];
+#pragma unroll
+        for (int j = 0; j < R0; ++j) x[j] = xin[j];
+        if (corr) {
+            const float* cr = corr + static_cast<size_t>(X) * corr_pitch + c.ra;
+            const float sg = ((c.s + t) & 1) ? -1.f : 1.f;       // column x0 + 256 j has the parity of x0
+            const cplx cc = cpack(sg * cr[0], c.has_b ? sg * cr[1] : 0.f);
+#pragma unroll
+            for (int j = 0; j < R0; ++j) x[j] = cadd(x[j], cc);
+        }
         int jlo, jhi;
         ols_item_range(t, ax.halo, c.nvalid, jlo, jhi);
         const int x0 = c.s + t;
@@ -400,6 +415,8 @@ struct OlsColIO {
     int nunits;
     OlsAxis ax;            // len = rows
     int b0;                // first block of this launch (the streamed host path launches block by block)
+    const float* corr;     // pffft Nyquist quirk, see OlsRowIO::corr: corr[ch * corr_pitch + column]
+    int corr_pitch;
 
     struct Ctx {
         uint8_t* ua;       // U byte of (ch, oct, row 0, 0)
@@ -447,8 +464,18 @@ struct OlsColIO {
     template <int R0>
     BLUR_HD void load_item(const Ctx&, int, int, cplx (&)[R0]) const {}
     template <int R0>
-    BLUR_HD void store_item(const Ctx& c, int X, int t, const cplx (&x)[R0]) const
+    BLUR_HD void store_item(const Ctx& c, int X, int t, const cplx (&xin)[R0]) const
     {
+        cplx x[R0];
+#pragma unroll
+        for (int j = 0; j < R0; ++j) x[j] = xin[j];
+        if (corr) {
+            const float* cr = corr + static_cast<size_t>(c.ch) * corr_pitch + c.oct * 8 + 2 * X;
+            const float sg = ((c.s + t) & 1) ? -1.f : 1.f;       // row s + t + 256 j has the parity of s + t
+            const cplx cc = cpack(sg * cr[0], sg * cr[1]);
+#pragma unroll
+            for (int j = 0; j < R0; ++j) x[j] = cadd(x[j], cc);
+        }
         int jlo, jhi;
         ols_item_range(t, ax.halo, c.nvalid, jlo, jhi);
         uint16_t* d = reinterpret_cast<uint16_t*>(c.ua + (static_cast<ptrdiff_t>(c.s + t) * 8 + 2 * X));

@@ -55,9 +55,10 @@ inline ShardGeom shard_geometry(const GaussGeometry& gg, int nyquist_mode, int r
 {
     ShardGeom g{};
     const int rows = gg.rows, cols = gg.cols;
-    // Overlap-save unless the Nyquist quirk of pffft is asked for (it is defined on the
-    // reference's full-length tile) or the kernel is too wide for the block menu.
-    int want_ols = nyquist_mode == 0 ? 1 : 0;
+    // Overlap-save unless the kernel is too wide for the block menu.  The Nyquist quirk of pffft
+    // (defined on the reference's full-length tile) is a rank-one correction per line that the
+    // overlap-save epilogues add on a single GPU; the sharded plan keeps the full-length kernel.
+    int want_ols = (nyquist_mode == 0 || nranks == 1) ? 1 : 0;
     if (const char* e = std::getenv("BLUR_B200_ALGO")) {
         if (!std::strcmp(e, "full")) want_ols = 0;
     }

@@ -166,7 +166,11 @@ def test_gauss_sharded_emulated_on_one_gpu(bb, torch):
             outs.append(oc)
         torch.cuda.synchronize()
         full = torch.cat(outs, 1)[:, :cols]
-        assert torch.equal(full, single), (rows, cols, P)
+        if mode == 0:
+            assert torch.equal(full, single), (rows, cols, P)
+        else:
+            # single GPU: overlap-save blocks + Nyquist correction; sharded: full-length kernel
+            assert (full.int() - single.int()).abs().max().item() <= 1, (rows, cols, P)
         for pl in plans + [p1]:
             pl.close()
 

@@ -73,10 +73,10 @@ def main():
 
     for name, rows, cols, sigma, mode in [
             ("C1 gauss 1080x1920 sigma=5 exact (pocketfft_1D semantics)", 1080, 1920, 5.0, bb.NYQUIST_EXACT),
-            ("C1 gauss 1080x1920 sigma=5 pffft quirk (pffft_, full-length kernel)", 1080, 1920, 5.0, bb.NYQUIST_PFFFT),
+            ("C1 gauss 1080x1920 sigma=5 pffft quirk (pffft_ semantics)", 1080, 1920, 5.0, bb.NYQUIST_PFFFT),
             ("C2 gauss 2160x3840 sigma=25 exact", 2160, 3840, 25.0, bb.NYQUIST_EXACT),
-            ("C2 gauss 2160x3840 sigma=25 pffft quirk (full-length kernel)", 2160, 3840, 25.0, bb.NYQUIST_PFFFT),
-            ("C3 gauss 16384x16384 sigma=50 pffft quirk (full-length kernel)", 16384, 16384, 50.0, bb.NYQUIST_PFFFT)]:
+            ("C2 gauss 2160x3840 sigma=25 pffft quirk (pffft_ semantics)", 2160, 3840, 25.0, bb.NYQUIST_PFFFT),
+            ("C3 gauss 16384x16384 sigma=50 pffft quirk (pffft_ semantics)", 16384, 16384, 50.0, bb.NYQUIST_PFFFT)]:
         d_in = torch.from_numpy(rng.integers(0, 256, (rows, cols, 3), dtype=np.uint8)).to(dev)
         d_out = torch.empty_like(d_in)
         plan = bb.GaussPlan(rows, cols, sigma, mode, device=0)
