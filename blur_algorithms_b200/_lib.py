@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libblur_b200.so")
+LIB_PATH = os.environ.get("BLUR_B200_LIB") or os.path.join(_HERE, "libblur_b200.so")   # env: experiment builds only
 
 OK, EINVAL, EPAD, ESIZE, ECUDA, ENOMEM = 0, 1, 2, 3, 4, 5
 NYQUIST_EXACT, NYQUIST_PFFFT = 0, 1
