@@ -54,6 +54,7 @@ def _load() -> C.CDLL:
         "blur_b200_gauss_rowpass_f32": (i32, [vp, vp, vp, vp]),
         "blur_b200_fastboxblur_device": (i32, [vp, i32, i32, i32, i32, i32, i32, vp, vp]),
         "blur_b200_fastboxblur": (i32, [vp, i32, i32, i32, i32, i32]),
+        "blur_b200_fastboxblur_batch_host": (i32, [vp, i32, i32, i32, i32, i32, i32]),
         "blur_b200_reflect_101_u8": (i32, [vp, vp, i32, i32, i32, i32, pi32, i32, vp]),
         "blur_b200_reflect_101_u8_host": (i32, [vp, vp, i32, i32, i32, i32, pi32, i32]),
         "blur_b200_deinterleave_u8_f32": (i32, [vp, vp, vp, vp, u32, vp]),
@@ -82,7 +83,7 @@ EXPORTED = [
     "blur_b200_gauss_plan_destroy", "blur_b200_gauss_plan_info", "blur_b200_gauss_run_device",
     "blur_b200_gauss_run_host", "blur_b200_gauss_run_host_batch", "blur_b200_gauss_u8c3", "blur_b200_gauss_row_pass",
     "blur_b200_gauss_col_pass", "blur_b200_gauss_row_pass_peer", "blur_b200_gauss_row_pass_push", "blur_b200_gauss_rowpass_f32", "blur_b200_fastboxblur_device",
-    "blur_b200_fastboxblur", "blur_b200_reflect_101_u8", "blur_b200_reflect_101_u8_host",
+    "blur_b200_fastboxblur", "blur_b200_fastboxblur_batch_host", "blur_b200_reflect_101_u8", "blur_b200_reflect_101_u8_host",
     "blur_b200_deinterleave_u8_f32", "blur_b200_interleave_f32_u8", "blur_b200_flip_block_f32",
     "blur_b200_deinterleave_u8_f32_host", "blur_b200_interleave_f32_u8_host", "blur_b200_flip_block_f32_host",
     "blur_b200_dft_image_device", "blur_b200_dft_image_host", "blur_b200_dft_image_sizes",

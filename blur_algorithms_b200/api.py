@@ -21,7 +21,7 @@ from ._lib import NYQUIST_EXACT, NYQUIST_PFFFT, BlurB200Error, check, lib
 __all__ = [
     "isValidSize", "nearestTransformSize", "gaussian_window", "getGaussian", "gauss_geometry",
     "pffft_", "pocketfft_1D", "pocketfft_2D", "fastboxblur", "Reflect_101", "deinterleave_BGR",
-    "interleave_BGR", "flip_block", "dft_image", "Test", "GaussPlan", "fastboxblur_device",
+    "interleave_BGR", "flip_block", "dft_image", "Test", "GaussPlan", "fastboxblur_device", "fastboxblur_batch",
     "kernel_launches", "BlurB200Error", "NYQUIST_EXACT", "NYQUIST_PFFFT",
 ]
 
@@ -197,6 +197,13 @@ def fastboxblur(image: np.ndarray, w: int, h: int, channels: int, ksize: int, pa
     if not image.flags["C_CONTIGUOUS"] or not image.flags["WRITEABLE"]:
         raise BlurB200Error(_lib.EINVAL, "image must be C-contiguous and writeable")
     check(lib.blur_b200_fastboxblur(image.ctypes.data, w, h, channels, int(ksize), int(passes)))
+
+
+def fastboxblur_batch(images, ksize: int, passes: int) -> None:
+    """`batch` images [batch, h, w, channels] (numpy uint8 or a pinned CPU torch tensor), each blurred
+    like fastboxblur(...) (Source.cpp:587), in place; uploads, kernels and downloads overlap."""
+    batch, h, w, channels = images.shape
+    check(lib.blur_b200_fastboxblur_batch_host(_ptr(images), w, h, channels, int(ksize), int(passes), batch))
 
 
 def fastboxblur_device(d_img, w: int, h: int, channels: int, ksize: int, passes: int, batch: int, d_scratch,

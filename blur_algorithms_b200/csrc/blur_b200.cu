@@ -1242,6 +1242,54 @@ int blur_b200_fastboxblur(uint8_t* h_img, int w, int h, int channels, int ksize,
     return rc;
 }
 
+// `batch` host images (contiguous, img bytes apart) streamed in groups: upload of group g+1, the
+// kernels of group g and the download of group g-1 overlap on three streams (two device slots).
+int blur_b200_fastboxblur_batch_host(uint8_t* h_imgs, int w, int h, int channels, int ksize, int passes, int batch)
+{
+    if (!h_imgs || w < 1 || h < 1 || channels < 1 || batch < 1) return BLUR_B200_EINVAL;
+    const size_t img_bytes = static_cast<size_t>(w) * h * channels;
+    const int group = static_cast<int>(std::max<size_t>(1, std::min<size_t>(batch, (256ull << 20) / img_bytes)));
+    uint8_t *d_img[2] = {}, *d_scr = nullptr;
+    cudaStream_t sh = nullptr, sc = nullptr, sd = nullptr;
+    cudaEvent_t up[2] = {}, done[2] = {}, down[2] = {};
+    int rc = BLUR_B200_OK;
+    auto cu = [&](cudaError_t e) { if (e != cudaSuccess && !rc) { g_cuda_err = cudaGetErrorString(e); rc = BLUR_B200_ECUDA; } return e == cudaSuccess; };
+    cu(cudaMalloc(&d_img[0], img_bytes * group)); cu(cudaMalloc(&d_img[1], img_bytes * group)); cu(cudaMalloc(&d_scr, img_bytes * group));
+    cu(cudaStreamCreateWithFlags(&sh, cudaStreamNonBlocking)); cu(cudaStreamCreateWithFlags(&sc, cudaStreamNonBlocking));
+    cu(cudaStreamCreateWithFlags(&sd, cudaStreamNonBlocking));
+    for (int k = 0; k < 2; ++k) {
+        cu(cudaEventCreateWithFlags(&up[k], cudaEventDisableTiming)); cu(cudaEventCreateWithFlags(&done[k], cudaEventDisableTiming));
+        cu(cudaEventCreateWithFlags(&down[k], cudaEventDisableTiming));
+    }
+    for (int b0 = 0, g = 0; b0 < batch && !rc; b0 += group, ++g) {
+        const int nb = std::min(group, batch - b0), k = g & 1;
+        uint8_t* hp = h_imgs + static_cast<size_t>(b0) * img_bytes;
+        if (g >= 2) cu(cudaStreamWaitEvent(sh, down[k], 0));            // slot k has been downloaded
+        cu(cudaMemcpyAsync(d_img[k], hp, img_bytes * nb, cudaMemcpyHostToDevice, sh));
+        cu(cudaEventRecord(up[k], sh));
+        cu(cudaStreamWaitEvent(sc, up[k], 0));
+        if (!rc) rc = blur_b200_fastboxblur_device(d_img[k], w, h, channels, ksize, passes, nb, d_scr, sc);
+        cu(cudaEventRecord(done[k], sc));
+        cu(cudaStreamWaitEvent(sd, done[k], 0));
+        cu(cudaMemcpyAsync(hp, d_img[k], img_bytes * nb, cudaMemcpyDeviceToHost, sd));
+        cu(cudaEventRecord(down[k], sd));
+    }
+    if (sd) cu(cudaStreamSynchronize(sd));
+    if (sc) cu(cudaStreamSynchronize(sc));
+    if (sh) cu(cudaStreamSynchronize(sh));
+    for (int k = 0; k < 2; ++k) {
+        cudaFree(d_img[k]);
+        if (up[k]) cudaEventDestroy(up[k]);
+        if (done[k]) cudaEventDestroy(done[k]);
+        if (down[k]) cudaEventDestroy(down[k]);
+    }
+    cudaFree(d_scr);
+    if (sh) cudaStreamDestroy(sh);
+    if (sc) cudaStreamDestroy(sc);
+    if (sd) cudaStreamDestroy(sd);
+    return rc;
+}
+
 // ---- layout utilities
 
 int blur_b200_reflect_101_u8(const uint8_t* d_in, uint8_t* d_out, int top, int bottom, int left, int right,

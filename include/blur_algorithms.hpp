@@ -98,6 +98,9 @@ inline void pocketfft_2D_DFT_image(uint8_t* image_data, int rows, int cols, doub
 // FastBoxBlur's entry as called at Source.cpp:587: in place.
 inline void fastboxblur(uint8_t* in, int w, int h, int channels, int ksize, int passes)
 { blur_b200::check(blur_b200_fastboxblur(in, w, h, channels, ksize, passes), "fastboxblur"); }
+// `batch` contiguous images, streamed (uploads / kernels / downloads overlap)
+inline void fastboxblur_batch(uint8_t* in, int w, int h, int channels, int ksize, int passes, int batch)
+{ blur_b200::check(blur_b200_fastboxblur_batch_host(in, w, h, channels, ksize, passes, batch), "fastboxblur_batch"); }
 
 // Utils.hpp:212-243.  Any trivially copyable T: a pixel is C*sizeof(T) bytes and reflection only
 // moves whole pixels.  original_size = {rows, cols}; pads are clamped to dim-1 like the reference.

@@ -152,6 +152,9 @@ int blur_b200_gauss_rowpass_f32(blur_b200_plan *plan, const uint8_t *d_in, float
 int blur_b200_fastboxblur_device(uint8_t *d_img, int w, int h, int channels, int ksize, int passes,
                                  int batch, uint8_t *d_scratch /* batch*w*h*channels bytes */, void *stream);
 int blur_b200_fastboxblur(uint8_t *h_img, int w, int h, int channels, int ksize, int passes);
+/* `batch` contiguous host images (the C5 workload; the reference calls fastboxblur once per image,
+ * Source.cpp:587), streamed in groups: uploads, kernels and downloads overlap.  In place. */
+int blur_b200_fastboxblur_batch_host(uint8_t *h_imgs, int w, int h, int channels, int ksize, int passes, int batch);
 
 /* ---- layout utilities (device pointers) ------------------------------------------------------ */
 /* Reflect_101<uint8_t,C>, Utils.hpp:212-243.  original_size = {rows, cols}.  Pads are clamped to

@@ -339,3 +339,31 @@ def test_dft_image_4096_single_plane_shape(bb, oracle):
     out = bb.dft_image(img, 0.1)
     ref = oracle.dft_image(img, 0.1)
     assert lsb(out, ref) <= 1
+
+
+def test_cli_flags_match_api(bb, oracle, tmp_path):
+    """`main flag nsmooth file` (Source.cpp:611-641) through blur_algorithms_b200.cli == the API calls."""
+    from blur_algorithms_b200 import cli
+    img = synth("noise", 96, 128, 5)
+    src = str(tmp_path / "in.ppm")
+    cli.write_image(src, img)
+    for flag, sigma in ((5, 3.0), (3, 3.0), (2, 3.0), (4, 3.0)):
+        out = str(tmp_path / f"out{flag}.ppm")
+        assert cli.main([str(flag), str(sigma), src, "-o", out]) == 0
+        got = cli.read_image(out)
+        want = img.copy()
+        cli.run_test(want, flag, sigma)
+        assert np.array_equal(got, want), flag
+        if flag == 5:
+            assert lsb(got, oracle.gauss_blur_1d(img, sigma, 0)) <= 1
+        if flag == 4:
+            assert np.array_equal(got, oracle.fastboxblur(img, 9, 2))
+
+
+def test_box_batch_host_streamed(bb, oracle):
+    """blur_b200_fastboxblur_batch_host: grouped three-stream pipeline == per-image calls (bit-exact)."""
+    imgs = np.stack([synth("noise", 270, 480, 40 + i) for i in range(5)])
+    want = np.stack([oracle.fastboxblur(im, 9, 2) for im in imgs])
+    got = imgs.copy()
+    bb.fastboxblur_batch(got, 9, 2)
+    assert np.array_equal(got, want)

@@ -186,3 +186,14 @@ def test_sharded_host_logic_gloo_world2(tmp_path):
     outs = [p.communicate(timeout=300)[0].decode() for p in procs]
     for p, o in zip(procs, outs):
         assert p.returncode == 0, o
+
+
+def test_cli_ppm_roundtrip(tmp_path):
+    """CLI image I/O (reference: cv::imread / cv::imwrite, Source.cpp:621,636): P6 round trip, BGR order."""
+    from blur_algorithms_b200 import cli
+    img = np.random.default_rng(3).integers(0, 256, (7, 5, 3), dtype=np.uint8)
+    p = str(tmp_path / "a.ppm")
+    cli.write_image(p, img)
+    assert open(p, "rb").read(2) == b"P6"
+    assert np.array_equal(cli.read_image(p), img)
+    assert cli.resize(img, 14, 10).shape == (14, 10, 3)
