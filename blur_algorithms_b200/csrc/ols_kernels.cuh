@@ -50,7 +50,11 @@ template <int R0> constexpr int ols_row_smem_bytes() { return 272 * R0 * 8 + 2 *
 template <int R0> constexpr int ols_row_ctas_per_sm()
 {
     constexpr int by_smem = (227 * 1024) / (ols_row_smem_bytes<R0>() + 1024);
+#ifdef BLUR_OLS_ROW_MINB
+    constexpr int by_regs = BLUR_OLS_ROW_MINB;                // experiment knob
+#else
     constexpr int by_regs = 512 / ols_row_threads<R0>();      // <= 128 registers per thread
+#endif
     constexpr int c = by_smem < by_regs ? by_smem : by_regs;
     return c < 1 ? 1 : c;
 }
