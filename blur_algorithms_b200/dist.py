@@ -102,7 +102,7 @@ class ShardedGaussBlur:
         # "push": row pass in chunks + copy kernel over peer mappings (default); "store": the row
         # kernel's epilogue stores remotely itself.  BLUR_B200_EXCHANGE overrides.
         self.exchange_mode = exchange_mode or os.environ.get("BLUR_B200_EXCHANGE", "push")
-        self.nchunks = nchunks or int(os.environ.get("BLUR_B200_CHUNKS", "0")) or {2: 12, 4: 4}.get(self.nranks, 2)
+        self.nchunks = nchunks or int(os.environ.get("BLUR_B200_CHUNKS", "0")) or {2: 12}.get(self.nranks, 2)
         self.q_send = None
         want_fused = (fused is not False and row_pass is None and col_pass is None and self.nranks > 1
                       and self.nranks <= 8 and g.algo == 1 and self.device.type == "cuda")

@@ -224,6 +224,28 @@ def test_gauss_full_size_properties(bb, oracle, torch, rows, cols, sigma):
     plan.close()
 
 
+def test_gauss_pffft_mode_full_size_block_vs_full_length(bb, torch, monkeypatch):
+    """pffft_ semantics at BASELINE config 3: overlap-save blocks + per-line Nyquist correction
+     against the full-length kernel that scales bin N/2 itself (Source.cpp:420-426)."""
+    rows = cols = 16384
+    img = torch.from_numpy(np.random.default_rng(1).integers(0, 256, (rows, cols, 3), dtype=np.uint8)).cuda()
+    p_blk = bb.GaussPlan(rows, cols, 50.0, bb.NYQUIST_PFFFT)
+    assert p_blk.info["algo"] == 1
+    a = torch.empty_like(img)
+    p_blk.run(img, a)
+    torch.cuda.synchronize()
+    p_blk.close()
+    monkeypatch.setenv("BLUR_B200_ALGO", "full")
+    p_full = bb.GaussPlan(rows, cols, 50.0, bb.NYQUIST_PFFFT)
+    assert p_full.info["algo"] == 0
+    b = torch.empty_like(img)
+    p_full.run(img, b)
+    torch.cuda.synchronize()
+    p_full.close()
+    d = (a.to(torch.int16) - b.to(torch.int16)).abs()
+    assert int(d.max()) <= 1 and float((d > 0).float().mean()) < 1e-2
+
+
 def test_gauss_4k_vs_oracle(bb, oracle):
     """BASELINE config 2 in full against the oracle (a few seconds of CPU)."""
     img = synth("noise", 2160, 3840, 0)
