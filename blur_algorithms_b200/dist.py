@@ -137,6 +137,11 @@ class ShardedGaussBlur:
     def run(self, in_stripe: torch.Tensor) -> torch.Tensor:
         """in_stripe: uint8 [valid_rows, cols, 3] (this rank's rows).  Returns this rank's column
         stripe of the result, uint8 [rows, valid_cols, 3] (a view into an internal buffer)."""
+        self._rows(in_stripe)
+        return self._cols()
+
+    def _rows(self, in_stripe: torch.Tensor) -> None:
+        """row pass of this rank's stripe + the exchange (the distributed flip_block, Source.cpp:540)"""
         if self.symm is not None:
             # peers may still be reading their buffers (previous blur's column pass)
             self.symm.barrier(channel=0)
@@ -150,5 +155,47 @@ class ShardedGaussBlur:
             if self.geom.valid_rows > 0:
                 self._row_pass(in_stripe, self.q_send)
             exchange(self.q_send, self.q_recv, self.group, self.geom.algo)
+
+    def _cols(self) -> torch.Tensor:
         self._col_pass(self.q_recv, self.out_cols)
         return self.out_cols[:, : self.geom.valid_cols]
+
+    def run_host_stream(self, h_ins: list, h_outs: list) -> None:
+        """Stream images through the sharded blur from host memory: h_ins[i] = this rank's row stripe of
+        image i (pinned uint8 [valid_rows, cols, 3]), h_outs[i] = pinned uint8 [rows, 2*cpp, 3] receiving
+        this rank's column stripe.  The upload of image i+1 runs under the kernels and the download of
+        image i (separate streams, double-buffered input stripe); the column pass of image i+1 waits
+        for the download of image i because the result buffer is single."""
+        if len(h_ins) != len(h_outs):
+            raise ValueError("h_ins and h_outs must have the same length")
+        cur = torch.cuda.current_stream(self.device)
+        if not hasattr(self, "_s_up"):
+            self._s_up = torch.cuda.Stream(self.device)
+            self._s_dn = torch.cuda.Stream(self.device)
+            self._d_in = [torch.empty((self.geom.valid_rows, self.geom.cols, 3), dtype=torch.uint8, device=self.device)
+                          for _ in range(2)]
+        ev_up = [torch.cuda.Event(), torch.cuda.Event()]
+        ev_row = [torch.cuda.Event(), torch.cuda.Event()]
+        ev_dn = None
+        for i, (hi, ho) in enumerate(zip(h_ins, h_outs)):
+            k = i & 1
+            with torch.cuda.stream(self._s_up):
+                if i >= 2:
+                    self._s_up.wait_event(ev_row[k])     # the row pass of image i-2 has read this slot
+                self._d_in[k].copy_(hi, non_blocking=True)
+                ev_up[k].record(self._s_up)
+            cur.wait_event(ev_up[k])
+            self._rows(self._d_in[k])
+            ev_row[k].record(cur)
+            if ev_dn is not None:
+                cur.wait_event(ev_dn)                    # image i-1 has left out_cols
+            self._cols()
+            ev_c = torch.cuda.Event()
+            ev_c.record(cur)
+            with torch.cuda.stream(self._s_dn):
+                self._s_dn.wait_event(ev_c)
+                ho.copy_(self.out_cols, non_blocking=True)
+                ev_dn = torch.cuda.Event()
+                ev_dn.record(self._s_dn)
+        self._s_dn.synchronize()
+        cur.synchronize()

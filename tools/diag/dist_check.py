@@ -25,6 +25,14 @@ for rows, cols, sigma in [(1080, 1920, 5.0), (2160, 3840, 25.0), (1001, 1531, 9.
     ref = plan.run(full, torch.empty_like(full))
     mine = ref[:, g.col0:g.col0 + g.valid_cols]
     same = bool(torch.equal(mine, out_cols)) if g.valid_cols > 0 else True
+    # streamed host path: three different images through run_host_stream == run() on each
+    imgs = [np.random.default_rng(70 + i).integers(0, 256, (rows, cols, 3), dtype=np.uint8) for i in range(3)]
+    h_ins = [torch.from_numpy(im[g.row0:g.row0 + g.valid_rows].copy()).pin_memory() for im in imgs]
+    h_outs = [torch.empty((rows, 2 * g.cpp, 3), dtype=torch.uint8).pin_memory() for _ in imgs]
+    sb.run_host_stream(h_ins, h_outs)
+    for hi, ho in zip(h_ins, h_outs):
+        want = sb.run(hi.to(dev)).clone()
+        same = same and bool(torch.equal(want.cpu(), ho[:, :g.valid_cols]))
     t = torch.tensor([int(same)], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     if rank == 0:
