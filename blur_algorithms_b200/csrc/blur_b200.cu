@@ -292,46 +292,77 @@ quirk_rows_kernel(const uint8_t* __restrict__ in, int cols, int pad, double c, f
         static_cast<float>(c * static_cast<double>(part[0][tid] + part[1][tid] + part[2][tid] + part[3][tid]));
 }
 
-// columns of Q [3][srows][qpitch] (single GPU), two steps with a fixed summation order:
-// quirk_cols_partial: block (32 column quads, 8 row lanes), grid (ceil(qpitch/128), 3, kQuirkSeg row
-// segments), float4 loads, double accumulators -> part[seg][ch][col];  quirk_cols_final: corr = c * sum.
-constexpr int kQuirkSeg = 8;
-__global__ void __launch_bounds__(256)
-quirk_cols_partial(const float* __restrict__ q, int rows, int srows, int qpitch, int pad, double* __restrict__ partial)
+// columns: A_col[ch][x] = sum_r w_r (-1)^r Q[ch][r][x] without sweeping Q.  The row pass is linear,
+// Q[r][x] = rowblur(in[r])[x] + (-1)^x corr_row[r], so
+//   A_col[x] = rowblur(S)[x] + (-1)^x * sum_r w_r (-1)^r corr_row[r],   S[x] = sum_r w_r (-1)^r in[r][x]
+// S is an exact integer line (one sweep over the uint8 image, 3 B/px), its reflect-101 row blur a
+// direct convolution with the taps in double (cols x ksize products).
+constexpr int kQuirkSeg = 64;      // maximum; a launch uses nseg = clamp(rows / 128, 1, kQuirkSeg) row segments
+// byte columns j of the interleaved image: partial[seg][j] = sum over the segment's rows of w_r (-1)^r in[r][j].
+// grid (ceil(pitch/4/128), kQuirkSeg), 128 threads, one 32-bit word column per thread (vec) or one byte column.
+__global__ void __launch_bounds__(128)
+quirk_insum_partial(const uint8_t* __restrict__ in, int rows, int pitch /* cols*3 */, int pad, int* __restrict__ partial, int vec)
 {
-    __shared__ double sm[8][32][4];
-    const int col = (blockIdx.x * 32 + threadIdx.x) * 4, ch = blockIdx.y, ry = threadIdx.y;
-    const int seg_rows = (rows + kQuirkSeg - 1) / kQuirkSeg;
-    const int r_begin = blockIdx.z * seg_rows, r_end = min(rows, r_begin + seg_rows);
-    double a0 = 0, a1 = 0, a2 = 0, a3 = 0;
-    if (col < qpitch) {
-        const float* p = q + static_cast<size_t>(ch) * srows * qpitch + col;
+    const int seg_rows = (rows + gridDim.y - 1) / gridDim.y;
+    const int r_begin = blockIdx.y * seg_rows, r_end = min(rows, r_begin + seg_rows);
+    const int j = (blockIdx.x * 128 + threadIdx.x) * (vec ? 4 : 1);
+    if (j >= pitch) return;
+    int* out = partial + static_cast<size_t>(blockIdx.y) * pitch + j;
+    if (vec) {
+        int a0 = 0, a1 = 0, a2 = 0, a3 = 0;
 #pragma unroll 4
-        for (int r = r_begin + ry; r < r_end; r += 8) {
-            const float4 v = __ldg(reinterpret_cast<const float4*>(p + static_cast<size_t>(r) * qpitch));
-            const double w = quirk_weight(r, rows, pad) * ((r & 1) ? -1 : 1);
-            a0 += w * v.x; a1 += w * v.y; a2 += w * v.z; a3 += w * v.w;
+        for (int r = r_begin; r < r_end; ++r) {
+            const uint32_t v = __ldg(reinterpret_cast<const uint32_t*>(in + static_cast<size_t>(r) * pitch + j));
+            const int w = (quirk_weight(r, rows, pad) * ((r & 1) ? -1 : 1)) & 0xff;
+            a0 = dp4a_us(v, w, a0); a1 = dp4a_us(v, w << 8, a1); a2 = dp4a_us(v, w << 16, a2); a3 = dp4a_us(v, w << 24, a3);
         }
-    }
-    sm[ry][threadIdx.x][0] = a0; sm[ry][threadIdx.x][1] = a1; sm[ry][threadIdx.x][2] = a2; sm[ry][threadIdx.x][3] = a3;
-    __syncthreads();
-    const int t = ry * 32 + threadIdx.x;           // 128 columns of this block
-    if (t < 128 && blockIdx.x * 128 + t < qpitch) {
-        double s = 0;
-#pragma unroll
-        for (int k = 0; k < 8; ++k) s += sm[k][t >> 2][t & 3];
-        partial[(static_cast<size_t>(blockIdx.z) * 3 + ch) * qpitch + blockIdx.x * 128 + t] = s;
+        out[0] = a0; out[1] = a1; out[2] = a2; out[3] = a3;
+    } else {
+        int a0 = 0;
+        for (int r = r_begin; r < r_end; ++r)
+            a0 += quirk_weight(r, rows, pad) * ((r & 1) ? -1 : 1) * in[static_cast<size_t>(r) * pitch + j];
+        out[0] = a0;
     }
 }
 
-__global__ void quirk_cols_final(const double* __restrict__ partial, int n /* 3 * qpitch */, double c, float* __restrict__ corr)
+// corr_col[ch * qpitch + x] = c_col * ( sum_k taps[|k|] S[refl101(x + k)][ch] + (-1)^x rsum[ch] ),  k = -pad..pad,
+// rsum[ch] = sum_r w_r (-1)^r corr_row[ch][r], S = sum of the segment partials.  grid (ceil(cols/128), 3),
+// 128 threads; every CTA reduces rsum itself (fixed order) and stages its 128 + 2 pad values of S
+// in shared memory (dynamic, (128 + 2 pad) ints).
+__global__ void __launch_bounds__(128)
+quirk_col_corr(const int* __restrict__ partial, int cols, int rows, int pad, const double* __restrict__ taps /* [pad+1] */,
+               const float* __restrict__ corr_row, double c, float* __restrict__ corr, int qpitch, int nseg)
 {
-    const int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    double s = 0;
-#pragma unroll
-    for (int k = 0; k < kQuirkSeg; ++k) s += partial[static_cast<size_t>(k) * n + i];
-    corr[i] = static_cast<float>(c * s);
+    extern __shared__ int sS[];
+    __shared__ double red[128];
+    const int tid = threadIdx.x, ch = blockIdx.y, x0 = blockIdx.x * 128;
+    const int pitch = cols * 3;
+    const float* cr = corr_row + static_cast<size_t>(ch) * rows;
+    double a = 0;
+    for (int r = tid; r < rows; r += 128) a += static_cast<double>(cr[r]) * (quirk_weight(r, rows, pad) * ((r & 1) ? -1 : 1));
+    red[tid] = a;
+    for (int e = tid; e < 128 + 2 * pad; e += 128) {
+        int xs = x0 - pad + e;
+        if (xs < 0) xs = -xs;
+        if (xs >= cols) xs = 2 * (cols - 1) - xs;
+        int sv = 0;
+        if (xs >= 0 && xs < cols) {
+#pragma unroll 4
+            for (int g = 0; g < nseg; ++g) sv += partial[static_cast<size_t>(g) * pitch + 3 * xs + ch];
+        }
+        sS[e] = sv;
+    }
+    __syncthreads();
+    for (int d = 64; d; d >>= 1) {
+        if (tid < d) red[tid] += red[tid + d];
+        __syncthreads();
+    }
+    const int x = x0 + tid;
+    if (x >= cols) return;
+    double acc = taps[0] * static_cast<double>(sS[tid + pad]);
+    for (int k = 1; k <= pad; ++k) acc += taps[k] * (static_cast<double>(sS[tid + pad - k]) + static_cast<double>(sS[tid + pad + k]));
+    acc += ((x & 1) ? -1.0 : 1.0) * red[0];
+    corr[static_cast<size_t>(ch) * qpitch + x] = static_cast<float>(c * acc);
 }
 
 // ------------------------------------------------------------------ exchange kernel
@@ -528,7 +559,8 @@ struct blur_b200_plan {
     bool quirk_ols = false;
     double quirk_c_row = 0, quirk_c_col = 0;      // (K[0] - K[N/2]) / N of each axis
     float *d_corr_row = nullptr, *d_corr_col = nullptr;   // [3][rows], [3][qpitch]
-    double* d_corr_part = nullptr;                        // [kQuirkSeg][3][qpitch]
+    int* d_insum = nullptr;                               // [kQuirkSeg][cols*3] partial column sums of the input
+    double* d_taps = nullptr;                             // centred taps [pad+1]
     // streamed host path (blur_b200_gauss_run_host_batch), all lazy: input / output images double
     // buffered, one stream per PCIe direction, events (image parity x chunk)
     uint8_t* d_sin[2] = {};
@@ -655,7 +687,13 @@ int plan_create(blur_b200_plan** out, int rows, int cols, double sigma, int mode
             p->quirk_ols = true;
             CU_TRY(cudaMalloc(&p->d_corr_row, sizeof(float) * 3 * rows));
             CU_TRY(cudaMalloc(&p->d_corr_col, sizeof(float) * 3 * p->qpitch));
-            CU_TRY(cudaMalloc(&p->d_corr_part, sizeof(double) * 8 * 3 * p->qpitch));
+            CU_TRY(cudaMalloc(&p->d_insum, sizeof(int) * kQuirkSeg * 3 * static_cast<size_t>(cols)));
+            CU_TRY(cudaMemset(p->d_corr_col, 0, sizeof(float) * 3 * p->qpitch));
+            get_gaussian(taps, sigma, gg.ksize, gg.n_row);          // rotated: centre tap at 0, offset k at index k
+            std::vector<double> tc(static_cast<size_t>(gg.pad) + 1);
+            for (int k = 0; k <= gg.pad; ++k) tc[k] = taps[k];
+            CU_TRY(cudaMalloc(&p->d_taps, sizeof(double) * tc.size()));
+            CU_TRY(cudaMemcpy(p->d_taps, tc.data(), sizeof(double) * tc.size(), cudaMemcpyHostToDevice));
         }
     } else {
         rc = build_axis(p->row, gg.n_row, sigma, gg.ksize, mode);
@@ -670,6 +708,22 @@ int plan_create(blur_b200_plan** out, int rows, int cols, double sigma, int mode
     CU_TRY(cudaMalloc(&p->d_u, static_cast<size_t>(3) * 2 * p->cpp * rows));
     CU_TRY(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
     *out = p;
+    return BLUR_B200_OK;
+}
+
+// pffft-quirk plans: column corrections from the input image and the row corrections (all rows of
+// d_corr_row must have been produced on `st` before)
+int quirk_prepare_cols(blur_b200_plan* p, const uint8_t* d_in, cudaStream_t st)
+{
+    const int pitch = p->cols * 3;
+    const int vec = pitch % 4 == 0 && reinterpret_cast<uintptr_t>(d_in) % 4 == 0;
+    const int nseg = std::max(1, std::min(kQuirkSeg, p->rows / 128));
+    quirk_insum_partial<<<dim3(cdiv(vec ? pitch / 4 : pitch, 128), nseg), 128, 0, st>>>(d_in, p->rows, pitch, p->gg.pad, p->d_insum, vec);
+    CU_TRY(cudaGetLastError());
+    quirk_col_corr<<<dim3(cdiv(p->cols, 128), 3), 128, sizeof(int) * (128 + 2 * p->gg.pad), st>>>(
+        p->d_insum, p->cols, p->rows, p->gg.pad, p->d_taps, p->d_corr_row, p->quirk_c_col, p->d_corr_col, p->qpitch, nseg);
+    CU_TRY(cudaGetLastError());
+    g_launches += 2;
     return BLUR_B200_OK;
 }
 
@@ -690,6 +744,8 @@ int run_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, float* d_q, cuda
             CU_TRY(cudaGetLastError());
             ++g_launches;
             io.corr = p->d_corr_row; io.corr_pitch = p->rows;
+            const int rc = quirk_prepare_cols(p, d_in_stripe, st);
+            if (rc) return rc;
         }
         if (peers && p->nranks > 1) {
             io.peer = 1; io.rank = p->rank;
@@ -724,14 +780,6 @@ int run_col_pass_to_u(blur_b200_plan* p, const float* d_q_chunks, cudaStream_t s
         io.b0 = blk_begin;
         io.nunits = (blk_end - blk_begin) * 3 * io.noct;
         if (p->quirk_ols) {
-            if (blk_begin == 0) {
-                quirk_cols_partial<<<dim3(cdiv(p->qpitch, 128), 3, kQuirkSeg), dim3(32, 8), 0, st>>>(d_q_chunks, p->rows, p->stripe_rows,
-                                                                                                 p->qpitch, p->gg.pad, p->d_corr_part);
-                CU_TRY(cudaGetLastError());
-                quirk_cols_final<<<cdiv(3 * p->qpitch, 256), 256, 0, st>>>(p->d_corr_part, 3 * p->qpitch, p->quirk_c_col, p->d_corr_col);
-                CU_TRY(cudaGetLastError());
-                g_launches += 2;
-            }
             io.corr = p->d_corr_col; io.corr_pitch = p->qpitch;
         }
         CU_TRY(launch_ols_col(io, d_q_chunks, p->qpitch, p->nranks * p->stripe_rows, p->d_ols_twa_col, p->d_ols_twb,
@@ -851,7 +899,7 @@ void blur_b200_gauss_plan_destroy(blur_b200_plan* p)
     cudaFree(p->col.d_tw); cudaFree(p->col.d_kt);
     cudaFree(p->d_ols_twa_row); cudaFree(p->d_ols_twa_col); cudaFree(p->d_ols_twb);
     cudaFree(p->d_ols_kt_row); cudaFree(p->d_ols_kt_col);
-    cudaFree(p->d_q); cudaFree(p->d_u); cudaFree(p->d_corr_row); cudaFree(p->d_corr_col); cudaFree(p->d_corr_part);
+    cudaFree(p->d_q); cudaFree(p->d_u); cudaFree(p->d_corr_row); cudaFree(p->d_corr_col); cudaFree(p->d_insum); cudaFree(p->d_taps);
     for (uint8_t* b : p->d_sin) cudaFree(b);
     for (uint8_t* b : p->d_sout) cudaFree(b);
     if (p->h2d_stream) cudaStreamDestroy(p->h2d_stream);
@@ -974,6 +1022,10 @@ int blur_b200_gauss_run_host_batch(blur_b200_plan* p, const uint8_t* const* h_in
                 const int rc = run_row_pass(p, p->d_sin[k], p->d_q, sc);
                 if (rc) return rc;
             }
+        }
+        if (p->quirk_ols) {
+            const int rc = quirk_prepare_cols(p, p->d_sin[k], sc);
+            if (rc) return rc;
         }
         CU_TRY(cudaEventRecord(p->ev_rowdone[k], sc));
         if (i >= nbuf) CU_TRY(cudaStreamWaitEvent(sc, p->ev_d2hdone[k], 0));                 // image i-2 has left d_sout[k]
