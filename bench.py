@@ -330,7 +330,7 @@ def main() -> None:
             # (2) the headline: Ks images streamed through blur_b200_gauss_run_host_batch, every image
             # uploaded from and downloaded to pinned host memory inside the timed region; upload of
             # image i+1 / kernels of image i / download of image i-1 overlap (PCIe is full duplex)
-            Ks = max(4, min(K, 8))
+            Ks = max(4, min(K, 16))
             h_in2 = torch.from_numpy(np.ascontiguousarray(h_img.numpy()[::-1])).pin_memory()      # a second, different image
             h_out2 = torch.empty_like(h_img).pin_memory()
             ins = [(h_img if i % 2 == 0 else h_in2).numpy() for i in range(Ks)]
@@ -349,7 +349,7 @@ def main() -> None:
             g = sb.geom
             # every rank streams its row stripe in and its column stripe out through
             # ShardedGaussBlur.run_host_stream (upload of image i+1 under kernels / download of image i)
-            Ks = max(4, min(K, 8))
+            Ks = max(4, min(K, 16))
             h_out = torch.empty((rows, 2 * g.cpp, 3), dtype=torch.uint8).pin_memory()
             h_out2 = torch.empty_like(h_out).pin_memory()
             h_in2 = torch.flip(h_img, dims=[0]).contiguous().pin_memory()
