@@ -188,7 +188,8 @@ __device__ __forceinline__ uint8_t spec_to_u8(float v)
 __global__ void __launch_bounds__(kMaxThreads, 1)
 spec_cols_kernel(const __grid_constant__ FftGeom g, const __grid_constant__ ColsIO io,
                  const float2* __restrict__ tw, float* __restrict__ spec /* [3][H][W] or null */,
-                 uint8_t* __restrict__ out /* [rows][cols][3] */, int W, int rows, int cols, int top, int left)
+                 uint8_t* __restrict__ out /* [rows][cols][3] */, int W, int rows, int cols, int top, int left,
+                 uint8_t* __restrict__ Tq /* [3][WC][H] staging of the fast path, or null */)
 {
     extern __shared__ float2 smem[];
     const int T = blockDim.x, tid = threadIdx.x;
@@ -214,6 +215,30 @@ spec_cols_kernel(const __grid_constant__ FftGeom g, const __grid_constant__ Cols
     // k in [1, W/2-1] also col_ = W - k (cval = W/2 - col_ % (W/2)); col = col_ shifted by W/2
     const int colA = (k + W / 2) % W;
     const int colB = (k >= 1 && k <= W / 2 - 1) ? (W - k + W / 2) % W : -1;
+    if (Tq && !spec) {
+        // Fast path (uint8 image only): the column's H bytes are staged in shared memory in frequency
+        // order and leave as one contiguous run of Tq[ch][k][m]; spec_finish_kernel applies the
+        // shift / mirror / crop.  (Writing out[] from here costs one scattered byte store per pixel.)
+        float xr[32], xi[32];
+        const bool active = tid < H32;                     // blockDim >= H/32
+        if (active) {
+#pragma unroll
+            for (int j = 0; j < 32; ++j) { const float2 v = smem[tid * 33 + j]; xr[j] = v.x; xi[j] = v.y; }
+        }
+        __syncthreads();
+        uint8_t* sb = reinterpret_cast<uint8_t*>(smem);
+        if (active) {
+            Dft<32, false>::run(xr, xi);
+            const int mb = freq_base(g, tid);
+#pragma unroll
+            for (int q = 0; q < 32; ++q) sb[mb + q * H32] = spec_to_u8(20.f * log10f(fabsf(xr[q]) + 0.00001f));
+        }
+        __syncthreads();
+        uint4* dst = reinterpret_cast<uint4*>(Tq + (static_cast<size_t>(ch) * io.WC + k) * H);
+        const uint4* src = reinterpret_cast<const uint4*>(sb);
+        for (int i = tid; i < H / 16; i += T) dst[i] = src[i];
+        return;
+    }
     for (int u = tid; u < H32; u += T) {
         float xr[32], xi[32];
 #pragma unroll
@@ -242,6 +267,37 @@ spec_cols_kernel(const __grid_constant__ FftGeom g, const __grid_constant__ Cols
     }
 }
 
+// Tq [3][WC][H] (uint8, frequency order) -> out [rows][cols][3]: the reference's shift, column-only
+// mirror and crop (Source.cpp:244-247, 268-276).  block (32, 8), tile = 32 output columns x 32 rows,
+// transposed through shared memory: reads run along m (contiguous in Tq), writes along the
+// interleaved output row.
+__global__ void __launch_bounds__(256)
+spec_finish_kernel(const uint8_t* __restrict__ Tq, uint8_t* __restrict__ out, int H, int W, int WC, int rows, int cols,
+                   int top, int left)
+{
+    __shared__ uint8_t tile[3][32][33];
+    const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32, tx = threadIdx.x, ty = threadIdx.y;
+    const int r = r0 + tx;
+    const int m = (r + top + H / 2) % H;
+    for (int i = ty; i < 32; i += 8) {
+        const int c = c0 + i;
+        if (c < cols && r < rows) {
+            const int col_ = (c + left + W / 2) % W;
+            const int k = col_ <= W / 2 ? col_ : W - col_;
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch) tile[ch][i][tx] = Tq[(static_cast<size_t>(ch) * WC + k) * H + m];
+        }
+    }
+    __syncthreads();
+    for (int i = ty; i < 32; i += 8) {
+        const int rr = r0 + i, c = c0 + tx;
+        if (rr < rows && c < cols) {
+            uint8_t* o = out + (static_cast<size_t>(rr) * cols + c) * 3;
+            o[0] = tile[0][tx][i]; o[1] = tile[1][tx][i]; o[2] = tile[2][tx][i];
+        }
+    }
+}
+
 thread_local std::string g_err;
 #define CU_TRY(expr)                                                             \
     do {                                                                         \
@@ -259,6 +315,7 @@ thread_local std::string g_err;
 struct SpecWs {
     int device = -1, H = 0, W = 0;
     float2 *tww = nullptr, *twh = nullptr, *G = nullptr;
+    uint8_t* Tq = nullptr;
 };
 std::mutex g_ws_mutex;
 SpecWs g_ws;
@@ -300,7 +357,7 @@ int blur_b200_dft_image_device(const uint8_t* d_in, uint8_t* d_out, int rows, in
     if (g_ws.device != device || g_ws.H != gm.H || g_ws.W != gm.W) {
         if (g_ws.device >= 0) {
             CU_TRY(cudaDeviceSynchronize());
-            cudaFree(g_ws.tww); cudaFree(g_ws.twh); cudaFree(g_ws.G);
+            cudaFree(g_ws.tww); cudaFree(g_ws.twh); cudaFree(g_ws.G); cudaFree(g_ws.Tq);
             g_ws = SpecWs();
         }
         std::vector<float2> tw;
@@ -311,6 +368,7 @@ int blur_b200_dft_image_device(const uint8_t* d_in, uint8_t* d_out, int rows, in
         CU_TRY(cudaMalloc(&g_ws.twh, sizeof(float2) * tw.size()));
         CU_TRY(cudaMemcpy(g_ws.twh, tw.data(), sizeof(float2) * tw.size(), cudaMemcpyHostToDevice));
         CU_TRY(cudaMalloc(&g_ws.G, sizeof(float2) * static_cast<size_t>(3) * ((WC + 3) / 4) * 4 * gm.H));
+        CU_TRY(cudaMalloc(&g_ws.Tq, static_cast<size_t>(3) * WC * gm.H));
         g_ws.device = device; g_ws.H = gm.H; g_ws.W = gm.W;
     }
     float2 *d_tww = g_ws.tww, *d_twh = g_ws.twh, *d_G = g_ws.G;
@@ -323,8 +381,14 @@ int blur_b200_dft_image_device(const uint8_t* d_in, uint8_t* d_out, int rows, in
     CU_TRY(cudaGetLastError());
     ColsIO cio{d_G, gm.H, WC};
     spec_cols_kernel<<<3 * WC, threads_for(gm.H / 32), smem_h, st>>>(gh, cio, d_twh, d_spec_f32, d_out, gm.W, rows, cols,
-                                                                     gm.border[0], gm.border[2]);
+                                                                     gm.border[0], gm.border[2], g_ws.Tq);
     CU_TRY(cudaGetLastError());
+    if (!d_spec_f32) {
+        spec_finish_kernel<<<dim3((cols + 31) / 32, (rows + 31) / 32), dim3(32, 8), 0, st>>>(g_ws.Tq, d_out, gm.H, gm.W, WC, rows, cols,
+                                                                                        gm.border[0], gm.border[2]);
+        CU_TRY(cudaGetLastError());
+        blur_b200_count_launches(1);
+    }
     blur_b200_count_launches(2);
     CU_TRY(cudaStreamSynchronize(st));      // the shared workspace is free again when the call returns
     return BLUR_B200_OK;
