@@ -19,6 +19,7 @@
 
 #include <algorithm>
 #include <cstdint>
+#include <cstdlib>
 
 namespace blurb200 {
 
@@ -194,7 +195,13 @@ cudaError_t launch_box_fused_pass(const uint8_t* in, uint8_t* out, int w, int h,
     if ((pitch / 4) % 2 == 0) pitch += 4;                 // odd word pitch: 32 rows hit 32 different banks
     a.pitch = pitch;
     a.TY = 0;
+    static const int ty_env = std::getenv("BLUR_B200_BOX_TY") ? std::atoi(std::getenv("BLUR_B200_BOX_TY")) : 0;   // experiment knob
+    // 64-row tiles when four of them fit an SM (measured at r = 15: 6.45 -> 6.03 ms for 256 x 1080p against
+    // 96-row tiles, the kernel is occupancy-bound), else the tallest tile that fits
+    if (!ty_env && static_cast<size_t>(64 + 2 * r) * pitch <= 55u * 1024u) a.TY = 64;
     for (int ty : {96, 64, 32, 16}) {
+        if (a.TY) break;
+        if (ty_env && ty != ty_env) continue;
         const size_t need = static_cast<size_t>(ty + 2 * r) * pitch;
         if (need <= (ty == 96 ? 74u : 110u) * 1024u) { a.TY = ty; break; }
     }
