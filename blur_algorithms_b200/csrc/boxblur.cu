@@ -196,9 +196,18 @@ cudaError_t launch_box_fused_pass(const uint8_t* in, uint8_t* out, int w, int h,
     a.pitch = pitch;
     a.TY = 0;
     static const int ty_env = std::getenv("BLUR_B200_BOX_TY") ? std::atoi(std::getenv("BLUR_B200_BOX_TY")) : 0;   // experiment knob
-    // 64-row tiles when four of them fit an SM (measured at r = 15: 6.45 -> 6.03 ms for 256 x 1080p against
-    // 96-row tiles, the kernel is occupancy-bound), else the tallest tile that fits
-    if (!ty_env && static_cast<size_t>(64 + 2 * r) * pitch <= 55u * 1024u) a.TY = 64;
+    // The kernel is occupancy-bound (r = 15, 256 x 1080p: 96-row tiles / 3 resident CTAs 6.45 ms, 64 / 4 CTAs
+    // 6.03 ms, 62 / 5 CTAs 5.53 ms): take the most resident CTAs whose tile still has at least as many
+    // output rows as halo rows, then even the tiles out over the image height.
+    if (ty_env && static_cast<size_t>(ty_env + 2 * r) * pitch <= 110u * 1024u) a.TY = ty_env;
+    for (int n = 5; n >= 2 && !a.TY && !ty_env; --n) {
+        const int rows_fit = static_cast<int>((227u * 1024u / n - 1024u) / pitch);
+        const int ty = std::min(rows_fit - 2 * r, h);
+        if (ty >= 16 && ty >= 2 * r) {
+            const int tiles = (h + ty - 1) / ty;
+            a.TY = (h + tiles - 1) / tiles;
+        }
+    }
     for (int ty : {96, 64, 32, 16}) {
         if (a.TY) break;
         if (ty_env && ty != ty_env) continue;
