@@ -1056,15 +1056,36 @@ int blur_b200_gauss_run_host(blur_b200_plan* p, const uint8_t* h_in, uint8_t* h_
     return blur_b200_gauss_run_host_batch(p, &h_in, &h_out, 1);
 }
 
+// The one-shot entry keeps its last plan (tables, Q, U, staging images) so that a caller looping over
+// same-sized images — the reference's `Test` usage — pays for the plan once; a different geometry
+// replaces it.  Calls are serialised by the mutex.
+static std::mutex g_oneshot_mu;
+static blur_b200_plan* g_oneshot_plan = nullptr;
+
+void blur_b200_release_cached(void)
+{
+    std::lock_guard<std::mutex> lock(g_oneshot_mu);
+    if (g_oneshot_plan) blur_b200_gauss_plan_destroy(g_oneshot_plan);
+    g_oneshot_plan = nullptr;
+}
+
 int blur_b200_gauss_u8c3(uint8_t* h_bgr, int rows, int cols, double sigma, int nyquist_mode)
 {
-    blur_b200_plan* p = nullptr;
+    blur_b200_plan*& cached = g_oneshot_plan;
+    std::lock_guard<std::mutex> lock(g_oneshot_mu);
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess) { g_cuda_err = "cudaGetDevice failed (no CUDA device?)"; return BLUR_B200_ECUDA; }
-    int rc = blur_b200_gauss_plan_create(&p, rows, cols, sigma, nyquist_mode, dev);
-    if (rc) return rc;
-    rc = blur_b200_gauss_run_host(p, h_bgr, h_bgr);
-    blur_b200_gauss_plan_destroy(p);
+    if (cached && (cached->rows != rows || cached->cols != cols || cached->sigma != sigma || cached->mode != nyquist_mode ||
+                   cached->device != dev)) {
+        blur_b200_gauss_plan_destroy(cached);
+        cached = nullptr;
+    }
+    if (!cached) {
+        const int rc = blur_b200_gauss_plan_create(&cached, rows, cols, sigma, nyquist_mode, dev);
+        if (rc) { cached = nullptr; return rc; }
+    }
+    const int rc = blur_b200_gauss_run_host(cached, h_bgr, h_bgr);
+    if (rc) { blur_b200_gauss_plan_destroy(cached); cached = nullptr; }
     return rc;
 }
 

@@ -110,8 +110,11 @@ int blur_b200_gauss_run_host(blur_b200_plan *plan, const uint8_t *h_in, uint8_t 
 int blur_b200_gauss_run_host_batch(blur_b200_plan *plan, const uint8_t *const *h_in, uint8_t *const *h_out, int n);
 
 /* One-shot drop-in for `pffft_(image, sigma)` / `pocketfft_1D` / `pocketfft_2D` acting on
- * image.data in place (Source.cpp:429,280,143): creates a plan, runs, destroys. */
+ * image.data in place (Source.cpp:429,280,143).  The plan of the last geometry (tables and device
+ * workspaces, ~7 B/px + the float32 intermediate 12 B/px) stays cached for the next call of the same
+ * rows/cols/sigma/mode; blur_b200_release_cached() frees it.  Calls are serialised. */
 int blur_b200_gauss_u8c3(uint8_t *h_bgr, int rows, int cols, double sigma, int nyquist_mode);
+void blur_b200_release_cached(void);
 
 /* Pieces of the sharded pipeline (single-GPU plans accept them too, with nranks = 1):
  *   row pass : d_in_stripe = this rank's rows of the image (uint8 [valid rows][cols][3])

@@ -389,3 +389,17 @@ def test_box_batch_host_streamed(bb, oracle):
     got = imgs.copy()
     bb.fastboxblur_batch(got, 9, 2)
     assert np.array_equal(got, want)
+
+
+def test_oneshot_plan_cache(bb, oracle):
+    """blur_b200_gauss_u8c3 keeps its last plan: repeated and alternating geometries stay correct."""
+    from blur_algorithms_b200._lib import lib
+    a, b = synth("noise", 200, 300, 1), synth("noise", 160, 120, 2)
+    for img, sigma in ((a, 4.0), (a, 4.0), (b, 3.0), (a, 4.0), (a, 5.0)):
+        out = img.copy()
+        bb.pocketfft_1D(out, sigma)
+        assert lsb(out, oracle.gauss_blur_1d(img, sigma, 0)) <= 1
+    lib.blur_b200_release_cached()
+    out = b.copy()
+    bb.pffft_(out, 3.0)
+    assert lsb(out, oracle.gauss_blur_1d(b, 3.0, 1)) <= 1
