@@ -88,7 +88,7 @@ def resize(img: np.ndarray, rows: int, cols: int) -> np.ndarray:
     return np.ascontiguousarray(img[ri, ci])
 
 
-def run_test(image: np.ndarray, flag: int, nsmooth: float) -> float:
+def run_test(image: np.ndarray, flag: int, nsmooth: float, quiet: bool = False) -> float:
     """`Test(image, flag, nsmooth)` (Source.cpp:574-608): blurs `image` in place, returns elapsed ms."""
     import blur_algorithms_b200 as bb
     t0 = time.perf_counter()
@@ -107,7 +107,8 @@ def run_test(image: np.ndarray, flag: int, nsmooth: float) -> float:
             raise SystemExit("flag 1 is the reference's OpenCV baseline; cv2 is not importable here")
         cv2.GaussianBlur(image, (0, 0), nsmooth, dst=image)
     ms = (time.perf_counter() - t0) * 1e3
-    print(f"{NAMES.get(flag, 'OpenCV blur')}: {ms:f}")
+    if not quiet:
+        print(f"{NAMES.get(flag, 'OpenCV blur')}: {ms:f}")
     return ms
 
 
@@ -141,7 +142,7 @@ def sweep(image: np.ndarray, flag: int) -> None:
             plan.close()
         else:
             t0 = time.perf_counter()
-            run_test(img, flag, sigma if flag == 1 else round(math.sqrt(sigma)) | 1)
+            run_test(img, flag, sigma if flag == 1 else round(math.sqrt(sigma)) | 1, quiet=True)
             line["host_call_ms"] = (time.perf_counter() - t0) * 1e3
         line["megapixels_per_s"] = x * y / 1e3 / line.get("device_ms", line["host_call_ms"])
         print(json.dumps(line), flush=True)
