@@ -197,3 +197,27 @@ def test_oracle_vs_reference_live(oracle, reference):
         assert np.array_equal(oracle.gauss_blur_1d(im, sigma, 1), reference.test(im, 3, sigma))
         assert np.array_equal(oracle.gauss_blur_2d(im, sigma), reference.test(im, 2, sigma))
         assert np.array_equal(oracle.fastboxblur(im, 9, 2), reference.test(im, 4, 3.0))
+
+
+def test_pffft_quirk_is_rank_one_correction(oracle):
+    """The identity DESIGN.md 3.1a builds on: the oracle's pffft-mode row pass (Source.cpp:414-427)
+    equals the exact row pass + c (-1)^x A per line, A = weighted alternating sum of the line
+    (weight 2 on the reflect-mirrored samples), c = (K[0] - K[N/2]) / N."""
+    import blur_algorithms_b200 as bb
+    rows, cols, sigma = 24, 97, 4.0
+    img = np.random.default_rng(5).integers(0, 256, (rows, cols, 3), dtype=np.uint8)
+    _, rp_exact, _ = oracle.gauss_blur_1d(img, sigma, 0, want_f32=True)
+    _, rp_quirk, _ = oracle.gauss_blur_1d(img, sigma, 1, want_f32=True)
+    g = bb.gauss_geometry(rows, cols, sigma)
+    n, pad = g["n_row"], g["pad"]
+    taps = bb.getGaussian(sigma, g["kSize"], n).astype(np.float64)
+    sign = np.where(np.arange(n) % 2 == 0, 1.0, -1.0)
+    c = (taps.sum() - (taps * sign).sum()) / n
+    x = np.arange(cols)
+    w = 1.0 + ((x >= 1) & (x <= pad)) + ((x >= cols - 1 - pad) & (x <= cols - 2))
+    sx = np.where(x % 2 == 0, 1.0, -1.0)
+    planes = img.astype(np.float64).transpose(2, 0, 1)               # [3, rows, cols]
+    A = (planes * (w * sx)).sum(axis=2)                              # [3, rows]
+    want = rp_exact.astype(np.float64) + c * A[:, :, None] * sx[None, None, :]
+    assert np.abs(want - rp_quirk).max() < 2e-3
+    assert np.abs(rp_quirk - rp_exact).max() > 10 * 2e-3             # the correction is not negligible here
