@@ -10,6 +10,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <algorithm>
 #include <vector>
 
 #include "blur_algorithms.hpp"
@@ -93,6 +94,25 @@ int main(int argc, char** argv)
         plan.run(img.data(), b.data());
         pocketfft_1D(c.data(), rows, cols, nsmooth);
         expect(a == b && a == c, "GaussPlan reuse == one-shot call, in place == out of place");
+    }
+    {   // streamed batches: GaussPlan::run_batch and fastboxblur_batch == the per-image calls
+        blur_b200::GaussPlan plan(rows, cols, nsmooth);
+        const std::vector<uint8_t> img2 = synth(rows, cols, 2);
+        std::vector<uint8_t> a = img, b = img2, c = img, wa(img.size()), wb(img.size()), wc(img.size());
+        plan.run(img.data(), wa.data());
+        plan.run(img2.data(), wb.data());
+        const uint8_t* ins[3] = {a.data(), b.data(), c.data()};
+        uint8_t* outs[3] = {a.data(), b.data(), c.data()};
+        plan.run_batch(ins, outs, 3);
+        expect(a == wa && b == wb && c == wa, "GaussPlan::run_batch == run per image");
+        std::vector<uint8_t> two(2 * img.size()), x = img, y = img2;
+        std::copy(img.begin(), img.end(), two.begin());
+        std::copy(img2.begin(), img2.end(), two.begin() + img.size());
+        fastboxblur_batch(two.data(), cols, rows, 3, 25, 2, 2);
+        fastboxblur(x.data(), cols, rows, 3, 25, 2);
+        fastboxblur(y.data(), cols, rows, 3, 25, 2);
+        expect(std::equal(x.begin(), x.end(), two.begin()) && std::equal(y.begin(), y.end(), two.begin() + img.size()),
+               "fastboxblur_batch == fastboxblur per image");
     }
     {   // flag 4: fastboxblur(image.data, w, h, channels, nsmooth*nsmooth, 2) — bit exact
         std::vector<uint8_t> a = img, b = img;
