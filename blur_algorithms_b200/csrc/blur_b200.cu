@@ -552,6 +552,8 @@ struct blur_b200_plan {
     OlsAxis ols_row{}, ols_col{};
     float2 *d_ols_twa_row = nullptr, *d_ols_twa_col = nullptr, *d_ols_twb = nullptr;
     float *d_ols_kt_row = nullptr, *d_ols_kt_col = nullptr;
+    float2* d_ols2_tw = nullptr;      // two-factor kernels (ols2_kernels.cuh): twiddles and multipliers, shared by both axes
+    float* d_ols2_kt = nullptr;
     int qpitch = 0, cpart = 0;        // overlap-save Q: floats per row / image columns per part
     float* d_q = nullptr;             // [nranks] blocks
     uint8_t* d_u = nullptr;           // [3][2*cpp][rows]
@@ -635,6 +637,13 @@ int build_ols_tables(blur_b200_plan* p, double sigma, int ksize)
 {
     std::vector<float2> tw;
     std::vector<float> kt;
+    if (p->ols_row.R2 || p->ols_col.R2) {
+        make_ols2_tables(p->ols_row.R2 ? p->ols_row.R2 : p->ols_col.R2, sigma, ksize, tw, kt);
+        int rc2 = upload(&p->d_ols2_tw, tw);
+        if (rc2) return rc2;
+        if ((rc2 = upload(&p->d_ols2_kt, kt))) return rc2;
+        if (p->ols_row.R2 && p->ols_col.R2) return BLUR_B200_OK;
+    }
     make_ols_twiddles_b(tw);
     int rc = upload(&p->d_ols_twb, tw);
     if (rc) return rc;
@@ -711,6 +720,20 @@ int plan_create(blur_b200_plan** out, int rows, int cols, double sigma, int mode
     return BLUR_B200_OK;
 }
 
+// row / column FFT kernels of an overlap-save plan: two-factor (ols2) or three-factor instantiation
+cudaError_t launch_row_fft(blur_b200_plan* p, const OlsRowIO& io, int num_sms, cudaStream_t st)
+{
+    if (io.ax.R2) return launch_ols2_row(io, p->d_ols2_tw, p->d_ols2_kt, num_sms, st);
+    return launch_ols_row(io, p->d_ols_twa_row, p->d_ols_twb, p->d_ols_kt_row, num_sms, st);
+}
+
+// row pairs per wave of the persistent row grid (chunk granularity of the streamed / sharded paths)
+int row_wave_pairs(const blur_b200_plan* p)
+{
+    const int units = p->ols_row.R2 ? ols2_row_units_per_sm(p->ols_row.R2) : ols_resident_ctas(p->ols_row.R0);
+    return std::max(1, p->num_sms * units / std::max(1, p->ols_row.nblocks));
+}
+
 // pffft-quirk plans: column corrections from the input image and the row corrections (all rows of
 // d_corr_row must have been produced on `st` before)
 int quirk_prepare_cols(blur_b200_plan* p, const uint8_t* d_in, cudaStream_t st)
@@ -751,7 +774,7 @@ int run_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, float* d_q, cuda
             io.peer = 1; io.rank = p->rank;
             for (int k = 0; k < p->nranks; ++k) io.qpeer[k] = peers[k];
         }
-        CU_TRY(launch_ols_row(io, p->d_ols_twa_row, p->d_ols_twb, p->d_ols_kt_row, p->num_sms, st));
+        CU_TRY(launch_row_fft(p, io, p->num_sms, st));
         ++g_launches;
         return BLUR_B200_OK;
     }
@@ -778,12 +801,17 @@ int run_col_pass_to_u(blur_b200_plan* p, const float* d_q_chunks, cudaStream_t s
         io.ax = p->ols_col;
         if (blk_end < 0) blk_end = io.ax.nblocks;
         io.b0 = blk_begin;
-        io.nunits = (blk_end - blk_begin) * 3 * io.noct;
+        io.nbl = blk_end - blk_begin;
+        io.order = io.ax.R2 ? 1 : 0;
+        io.nunits = io.order ? io.nbl * 3 * 2 * cdiv(io.noct, 2) : io.nbl * 3 * io.noct;
         if (p->quirk_ols) {
             io.corr = p->d_corr_col; io.corr_pitch = p->qpitch;
         }
-        CU_TRY(launch_ols_col(io, d_q_chunks, p->qpitch, p->nranks * p->stripe_rows, p->d_ols_twa_col, p->d_ols_twb,
-                              p->d_ols_kt_col, p->num_sms, st));
+        if (io.ax.R2)
+            CU_TRY(launch_ols2_col(io, d_q_chunks, p->qpitch, p->nranks * p->stripe_rows, p->d_ols2_tw, p->d_ols2_kt, p->num_sms, st));
+        else
+            CU_TRY(launch_ols_col(io, d_q_chunks, p->qpitch, p->nranks * p->stripe_rows, p->d_ols_twa_col, p->d_ols_twb,
+                                  p->d_ols_kt_col, p->num_sms, st));
         ++g_launches;
         return BLUR_B200_OK;
     }
@@ -899,6 +927,7 @@ void blur_b200_gauss_plan_destroy(blur_b200_plan* p)
     cudaFree(p->col.d_tw); cudaFree(p->col.d_kt);
     cudaFree(p->d_ols_twa_row); cudaFree(p->d_ols_twa_col); cudaFree(p->d_ols_twb);
     cudaFree(p->d_ols_kt_row); cudaFree(p->d_ols_kt_col);
+    cudaFree(p->d_ols2_tw); cudaFree(p->d_ols2_kt);
     cudaFree(p->d_q); cudaFree(p->d_u); cudaFree(p->d_corr_row); cudaFree(p->d_corr_col); cudaFree(p->d_insum); cudaFree(p->d_taps);
     for (uint8_t* b : p->d_sin) cudaFree(b);
     for (uint8_t* b : p->d_sout) cudaFree(b);
@@ -984,7 +1013,7 @@ int blur_b200_gauss_run_host_batch(blur_b200_plan* p, const uint8_t* const* h_in
     const int npairs = cdiv(p->rows, 2);
     int nchunks = 1, wave_pairs = npairs, nwaves = 1;
     if (ols) {
-        wave_pairs = std::max(1, p->num_sms * ols_resident_ctas(p->ols_row.R0) / std::max(1, p->ols_row.nblocks));
+        wave_pairs = row_wave_pairs(p);
         nwaves = cdiv(npairs, wave_pairs);
         nchunks = std::max(1, std::min<int>(blur_b200_plan::kHostChunks, nwaves / 2));
     }
@@ -1016,7 +1045,7 @@ int blur_b200_gauss_run_host_batch(blur_b200_plan* p, const uint8_t* const* h_in
                     ++g_launches;
                     io.corr = p->d_corr_row + r0; io.corr_pitch = p->rows;
                 }
-                CU_TRY(launch_ols_row(io, p->d_ols_twa_row, p->d_ols_twb, p->d_ols_kt_row, p->num_sms, sc));
+                CU_TRY(launch_row_fft(p, io, p->num_sms, sc));
                 ++g_launches;
             } else {
                 const int rc = run_row_pass(p, p->d_sin[k], p->d_q, sc);
@@ -1138,7 +1167,7 @@ int blur_b200_gauss_row_pass_push(blur_b200_plan* p, const uint8_t* d_in_stripe,
         base[part] = part == rank ? q_peers[rank] : p->d_q + (static_cast<ptrdiff_t>(part) - rank) * static_cast<ptrdiff_t>(blk);
     // Chunks are whole waves of the persistent row grid (grid CTAs / blocks per line row pairs), so
     // cutting the stripe adds no partially filled wave except the stripe's own last one.
-    const int wave_pairs = std::max(1, p->num_sms * ols_resident_ctas(p->ols_row.R0) / std::max(1, p->ols_row.nblocks));
+    const int wave_pairs = row_wave_pairs(p);
     const int nwaves = cdiv(npairs, wave_pairs);
     nchunks = std::min(nchunks, nwaves);
     for (int c = 0; c < nchunks; ++c) {
@@ -1159,7 +1188,7 @@ int blur_b200_gauss_row_pass_push(blur_b200_plan* p, const uint8_t* d_in_stripe,
         static const int diag = std::getenv("BLUR_B200_PUSH_DIAG") ? std::atoi(std::getenv("BLUR_B200_PUSH_DIAG")) : 0;   // timing experiments only
         if (diag != 1) {
             static const int sms_free = std::getenv("BLUR_B200_ROW_SMS_FREE") ? std::atoi(std::getenv("BLUR_B200_ROW_SMS_FREE")) : 0;
-            CU_TRY(launch_ols_row(io, p->d_ols_twa_row, p->d_ols_twb, p->d_ols_kt_row, p->num_sms - (N > 1 ? sms_free : 0), st));
+            CU_TRY(launch_row_fft(p, io, p->num_sms - (N > 1 ? sms_free : 0), st));
             ++g_launches;
         }
         if (N == 1 || diag == 2) continue;

@@ -124,6 +124,30 @@ BLUR_HD cplx cfmai(cplx a, float c, cplx b)
              "mov.b64 cc, {%2, %2};\nfma.rn.f32x2 %0, s, cc, %1;\n}" : "=l"(d) : "l"(a), "f"(c), "l"(b));
     return d;
 }
+// a - c*b   (c real)
+BLUR_HD cplx cfmsr(cplx a, float c, cplx b)
+{
+    cplx d;
+    BLUR_ASM("{\n.reg .f32 x, y;\n.reg .b64 cc, n;\nmov.b64 {x, y}, %3;\nneg.f32 x, x;\nneg.f32 y, y;\nmov.b64 n, {x, y};\n"
+             "mov.b64 cc, {%2, %2};\nfma.rn.f32x2 %0, n, cc, %1;\n}" : "=l"(d) : "l"(a), "f"(c), "l"(b));
+    return d;
+}
+// a - i*c*b   (c real)  = a + {b.y, -b.x} * {c, c}
+BLUR_HD cplx cfmsi(cplx a, float c, cplx b)
+{
+    cplx d;
+    BLUR_ASM("{\n.reg .f32 x, y;\n.reg .b64 cc, s;\nmov.b64 {x, y}, %3;\nneg.f32 x, x;\nmov.b64 s, {y, x};\n"
+             "mov.b64 cc, {%2, %2};\nfma.rn.f32x2 %0, s, cc, %1;\n}" : "=l"(d) : "l"(a), "f"(c), "l"(b));
+    return d;
+}
+// 2a - s
+BLUR_HD cplx c2amb(cplx a, cplx s)
+{
+    cplx d;
+    BLUR_ASM("{\n.reg .f32 x, y, two;\n.reg .b64 cc, n;\nmov.b64 {x, y}, %2;\nneg.f32 x, x;\nneg.f32 y, y;\nmov.b64 n, {x, y};\n"
+             "mov.f32 two, 0f40000000;\nmov.b64 cc, {two, two};\nfma.rn.f32x2 %0, %1, cc, n;\n}" : "=l"(d) : "l"(a), "l"(s));
+    return d;
+}
 // a * w  = a * {wx, wx} + {-ay, ax} * {wy, wy}
 BLUR_HD cplx cmul(cplx a, cplx w)
 {
@@ -159,6 +183,9 @@ BLUR_HD cplx csubi(cplx a, cplx b) { return make_float2(a.x + b.y, a.y - b.x); }
 BLUR_HD cplx cscale(cplx a, float c) { return make_float2(a.x * c, a.y * c); }
 BLUR_HD cplx cfmar(cplx a, float c, cplx b) { return make_float2(fmaf(b.x, c, a.x), fmaf(b.y, c, a.y)); }
 BLUR_HD cplx cfmai(cplx a, float c, cplx b) { return make_float2(fmaf(b.y, -c, a.x), fmaf(b.x, c, a.y)); }
+BLUR_HD cplx cfmsr(cplx a, float c, cplx b) { return make_float2(fmaf(-b.x, c, a.x), fmaf(-b.y, c, a.y)); }
+BLUR_HD cplx cfmsi(cplx a, float c, cplx b) { return make_float2(fmaf(b.y, c, a.x), fmaf(-b.x, c, a.y)); }
+BLUR_HD cplx c2amb(cplx a, cplx s) { return make_float2(fmaf(a.x, 2.f, -s.x), fmaf(a.y, 2.f, -s.y)); }
 BLUR_HD cplx cmul(cplx a, cplx w) { return make_float2(fmaf(a.y, -w.y, a.x * w.x), fmaf(a.x, w.y, a.y * w.x)); }
 BLUR_HD cplx cmulc(cplx a, cplx w) { return make_float2(fmaf(a.y, w.y, a.x * w.x), fmaf(a.x, -w.y, a.y * w.x)); }
 #endif

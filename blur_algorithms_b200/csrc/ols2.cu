@@ -1,0 +1,54 @@
+// ols2.cu — instantiations and launchers of the two-factor overlap-save kernels.
+#include <algorithm>
+#include <cstdlib>
+#include "ols2_kernels.cuh"
+#include "ols_launch.hpp"
+
+namespace blurb200 {
+
+namespace {
+// The > 48 KB dynamic shared-memory opt-in is a per-device function attribute: set it before
+// every launch (it is a cheap host-side call) instead of caching a process-wide flag.
+template <class K>
+cudaError_t opt_in_smem(K kernel, int bytes)
+{
+    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, bytes);
+}
+}  // namespace
+
+cudaError_t launch_ols2_row(const OlsRowIO& io, const float2* tw2, const float* kt, int num_sms, cudaStream_t stream)
+{
+    if (io.ax.R2 != 32) return cudaErrorInvalidValue;
+    constexpr int R2 = 32;
+    constexpr int smem = ols2_row_smem_bytes<R2>();
+    cudaError_t e = opt_in_smem(ols2_row_kernel<R2>, smem);
+    if (e != cudaSuccess) return e;
+    static const int ctas_env = std::getenv("BLUR_B200_ROW_CTAS") ? std::atoi(std::getenv("BLUR_B200_ROW_CTAS")) : 0;
+    const int per_sm = ctas_env > 0 ? std::min(ctas_env, BLUR_OLS2_ROW_CTAS) : BLUR_OLS2_ROW_CTAS;
+    const int grid = std::min((io.nunits + kOls2RowWarps - 1) / kOls2RowWarps, num_sms * per_sm);
+    if (grid <= 0) return cudaSuccess;
+    ols2_row_kernel<R2><<<grid, 32 * kOls2RowWarps, smem, stream>>>(io, tw2, kt);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_ols2_col(const OlsColIO& io_in, const float* d_q, int qpitch, int rows_total, const float2* tw2,
+                            const float* kt, int num_sms, cudaStream_t stream)
+{
+    if (io_in.ax.R2 != 32) return cudaErrorInvalidValue;
+    constexpr int R2 = 32;
+    OlsColIO io = io_in;
+    io.q = d_q; io.qpitch = qpitch; io.rows_total = rows_total;
+    constexpr int smem = ols2_col_smem_bytes<R2>();
+    cudaError_t e = opt_in_smem(ols2_col_kernel<R2>, smem);
+    if (e != cudaSuccess) return e;
+    static const int ctas_env = std::getenv("BLUR_B200_COL_CTAS") ? std::atoi(std::getenv("BLUR_B200_COL_CTAS")) : 0;
+    const int per_sm = ctas_env > 0 ? std::min(ctas_env, BLUR_OLS2_COL_CTAS) : BLUR_OLS2_COL_CTAS;
+    const int grid = std::min(io.nunits, num_sms * per_sm);
+    if (grid <= 0) return cudaSuccess;
+    ols2_col_kernel<R2><<<grid, 128, smem, stream>>>(io, tw2, kt);
+    return cudaGetLastError();
+}
+
+int ols2_row_units_per_sm(int R2) { return R2 == 32 ? BLUR_OLS2_ROW_CTAS * kOls2RowWarps : 0; }
+
+}  // namespace blurb200

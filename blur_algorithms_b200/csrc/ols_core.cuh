@@ -54,6 +54,7 @@ struct OlsAxis {
     int nblocks;   // ceil(len / V)
     int len;       // line length (cols for the row pass, rows for the column pass)
     int pad;       // reflect-101 pad = (ksize - 1) / 2
+    int R2;        // 0: three-factor kernels (ols_kernels.cuh); 32: two-factor kernels, L = 32*R2 (ols2_kernels.cuh)
 };
 
 // reflect-101 source index of extended-line position g, or -1 where the reference's tile holds
@@ -415,6 +416,12 @@ struct OlsColIO {
     int nunits;
     OlsAxis ax;            // len = rows
     int b0;                // first block of this launch (the streamed host path launches block by block)
+    int nbl;               // order 1: blocks in this launch
+    int order;             // unit order.  0: octet fastest, then channel, then block (nunits = nbl*3*noct)
+                           // 1: member of an octet pair fastest, then block, then channel, then octet pair
+                           //    (nunits = nbl*3*2*ceil(noct/2)): the two halves of every 64-byte run of a Q row
+                           //    and the halo rows shared by vertically adjacent blocks are fetched at about the
+                           //    same time by neighbouring CTAs, so each reaches DRAM once
     const float* corr;     // pffft Nyquist quirk, see OlsRowIO::corr: corr[ch * corr_pitch + column]
     int corr_pitch;
 
@@ -424,15 +431,26 @@ struct OlsColIO {
         int s;             // row of tile index 0 (may be negative)
         int nvalid;        // outputs this block keeps: tile indices [halo, halo + nvalid)
         int ch, oct;
-        bool interior;
+        bool interior, valid;
     };
     BLUR_HD Ctx begin(int unit) const
     {
         Ctx c;
-        c.oct = unit % noct;
-        const int rest = unit / noct;
-        c.ch = rest % 3;
-        const int b = b0 + rest / 3;
+        int b;
+        if (order == 0) {
+            c.oct = unit % noct;
+            const int rest = unit / noct;
+            c.ch = rest % 3;
+            b = b0 + rest / 3;
+        } else {
+            const int u2 = unit >> 1;
+            b = b0 + u2 % nbl;
+            const int rest = u2 / nbl;
+            c.ch = rest % 3;
+            c.oct = 2 * (rest / 3) + (unit & 1);
+        }
+        c.valid = c.oct < noct;
+        if (!c.valid) c.oct = noct - 1;
         c.ua = u + (static_cast<size_t>(c.ch) * noct + c.oct) * rows * 8;
         c.qa = q + static_cast<size_t>(c.ch) * rows_total * qpitch + c.oct * 8;
         c.s = b * ax.V - ax.halo;

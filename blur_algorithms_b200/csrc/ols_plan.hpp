@@ -39,6 +39,19 @@ inline bool choose_ols_axis(int len, int pad, int align, int max_r0, OlsAxis& ax
     return ax.R0 != 0;
 }
 
+// Two-factor kernels (ols2_kernels.cuh): L = 32 * R2 with R2 = 32, halo = pad exactly.  Chosen when at
+// least `min_frac` of a block is valid output (narrow and medium kernels: sigma <= ~65); wider
+// kernels keep the three-factor kernels and their longer blocks.
+inline bool choose_ols2_axis(int len, int pad, OlsAxis& ax, double min_frac = 0.55)
+{
+    const int R2 = 32, L = 32 * R2;
+    const int V = L - 2 * pad;
+    if (V < static_cast<int>(min_frac * L)) return false;
+    ax = OlsAxis{};
+    ax.R0 = L / 256; ax.L = L; ax.halo = pad; ax.V = V; ax.nblocks = (len + V - 1) / V; ax.len = len; ax.pad = pad; ax.R2 = R2;
+    return true;
+}
+
 // How one image is cut over `nranks` GPUs (nranks = 1: the whole image) and which algorithm
 // runs: the single source of truth for blur_b200.cu, the CPU emulator and dist.py.
 struct ShardGeom {
@@ -67,6 +80,16 @@ inline ShardGeom shard_geometry(const GaussGeometry& gg, int nyquist_mode, int r
     if (want_ols && choose_ols_axis(cols, gg.pad, 1, 32, g.ols_row, force_r0) &&
         choose_ols_axis(rows, gg.pad, 1, 24, g.ols_col, force_r0))
         g.algo = 1;
+    // two-factor kernels where the kernel is narrow enough for their 1024-sample blocks
+    // (BLUR_B200_OLS2=0: keep the three-factor kernels; =row / =col: one axis only — A/B measurements)
+    if (g.algo == 1 && !force_r0) {
+        const char* e = std::getenv("BLUR_B200_OLS2");
+        const bool want_row = !e || !std::strcmp(e, "1") || !std::strcmp(e, "row");
+        const bool want_col = !e || !std::strcmp(e, "1") || !std::strcmp(e, "col");
+        OlsAxis a2;
+        if (want_row && choose_ols2_axis(cols, gg.pad, a2)) g.ols_row = a2;
+        if (want_col && choose_ols2_axis(rows, gg.pad, a2)) g.ols_col = a2;
+    }
     const int cp_total = (cols + 1) / 2;
     int sr = (rows + nranks - 1) / nranks;
     if (g.algo == 1) {
@@ -123,6 +146,26 @@ inline void make_ols_kt(int R0, double sigma, int ksize, std::vector<float>& kt)
             const int k = k0 + R0 * (k1 + 16 * q);
             kt[static_cast<size_t>(q) * W + u] = static_cast<float>(K[k]) * scaler;
         }
+}
+
+// Tables of the two-factor kernels (ols2_core.cuh), L = 32 * R2:
+//   tw2[j * 32 + t] = exp(-2 pi i j t / L),  j < R2, t < 32     (thread constants W_L^{t j})
+//   kt[k2 * 32 + k1] = Re K_L[k1 + 32 k2] * (1/L)               (same provenance as make_ols_kt)
+inline void make_ols2_tables(int R2, double sigma, int ksize, std::vector<float2>& tw2, std::vector<float>& kt)
+{
+    const int L = 32 * R2;
+    tw2.resize(static_cast<size_t>(R2) * 32);
+    for (int j = 0; j < R2; ++j)
+        for (int t = 0; t < 32; ++t) {
+            const double a = -2.0 * 3.14159265358979323846 * static_cast<double>(j) * t / L;
+            tw2[static_cast<size_t>(j) * 32 + t] = make_float2(static_cast<float>(std::cos(a)), static_cast<float>(std::sin(a)));
+        }
+    std::vector<double> K;
+    kernel_spectrum(sigma, ksize, L, K);
+    const float scaler = 1.f / static_cast<float>(L);
+    kt.resize(static_cast<size_t>(L));
+    for (int k2 = 0; k2 < R2; ++k2)
+        for (int k1 = 0; k1 < 32; ++k1) kt[static_cast<size_t>(k2) * 32 + k1] = static_cast<float>(K[k1 + 32 * k2]) * scaler;
 }
 
 }  // namespace blurb200

@@ -12,6 +12,7 @@
 #include "../../blur_algorithms_b200/csrc/blur_io.cuh"
 #include "../../blur_algorithms_b200/csrc/fft_dispatch.cuh"
 #include "../../blur_algorithms_b200/csrc/ols_plan.hpp"
+#include "../../blur_algorithms_b200/csrc/ols2_core.cuh"
 
 using namespace blurb200;
 
@@ -131,6 +132,83 @@ static void ols_col_units(const OlsColIO& io, const OlsTables& T)
     }
 }
 
+// ---- two-factor overlap-save path (ols2_core.cuh): the kernels' phases, one item after another ----
+struct Ols2Tables {
+    std::vector<float2> tw2;
+    std::vector<float> kt;
+    Ols2Tables(int R2, double sigma, int ksize) { make_ols2_tables(R2, sigma, ksize, tw2, kt); }
+    // thread constants of item t: w[j] = W_L^{t j}
+    template <int R2> void item_twiddles(int t, cplx (&w)[R2]) const
+    {
+        w[0] = cpack(1.f, 0.f);
+        for (int j = 1; j < R2; ++j) w[j] = tw2[static_cast<size_t>(j) * 32 + t];
+    }
+};
+
+template <int R2>
+static void ols2_row_units(const OlsRowIO& io, const Ols2Tables& T)
+{
+#pragma omp parallel
+    {
+        std::vector<float2> tile(static_cast<size_t>(ols2_tile_slots<R2>()));
+        std::vector<uint8_t> raw(2 * ols2_raw_pitch<R2>());
+        const uint8_t* lo = io.in;
+        const uint8_t* hi = io.in + static_cast<size_t>(io.rows) * io.cols * 3;
+#pragma omp for schedule(dynamic, 4)
+        for (int unit = 0; unit < io.nunits; ++unit) {
+            const OlsRowIO::Ctx ctx = io.begin(unit, raw.data(), ols2_raw_pitch<R2>());
+            std::fill(raw.begin(), raw.end(), 0xCD);
+            for (int k = 0; k < 2 && ctx.ra + k < io.rows; ++k) {
+                const OlsRowIO::Stage st = io.stage_of(ctx.ra + k, ctx.s, ctx.w0, ctx.w1);
+                for (int e = 0; e < 16 * st.nvec; ++e)
+                    if (st.src + e >= lo && st.src + e < hi) raw[k * ols2_raw_pitch<R2>() + st.dst + e] = st.src[e];
+            }
+            if (!ctx.interior)
+                for (int e = 0; e < 2 * ols2_len<R2>(); ++e) io.fixup(ctx, e);
+            for (int ch = 0; ch < 3; ++ch) {
+                std::fill(tile.begin(), tile.end(), make_float2(-777.f, 777.f));
+                for (int n2 = 0; n2 < R2; ++n2) ols2_row_pass1<R2>(tile.data(), ctx, ch, n2);
+                for (int k1 = 0; k1 < 32; ++k1) { cplx w[R2]; T.item_twiddles<R2>(k1, w); ols2_pass2<R2, 1>(tile.data(), k1, w, T.kt.data()); }
+                for (int n2 = 0; n2 < R2; ++n2) { cplx w[32]; T.item_twiddles<32>(n2, w); ols2_row_pass3<R2>(tile.data(), io, ctx, ch, n2, w); }
+            }
+        }
+    }
+}
+
+template <int R2>
+static void ols2_col_units(const OlsColIO& io, const Ols2Tables& T)
+{
+    constexpr int F = 4, L = ols2_len<R2>();
+#pragma omp parallel
+    {
+        std::vector<float2> smem(static_cast<size_t>(F) * ols2_tile_slots<R2>());
+#pragma omp for schedule(dynamic, 4)
+        for (int unit = 0; unit < io.nunits; ++unit) {
+            const OlsColIO::Ctx ctx = io.begin(unit);
+            if (!ctx.valid) continue;
+            std::fill(smem.begin(), smem.end(), make_float2(-777.f, 777.f));
+            for (int i = 0; i < L; ++i)
+                for (int X = 0; X < F; ++X) {
+                    const float* p = io.src(ctx, X, i);
+                    smem[static_cast<size_t>(F) * ols2_slot<R2>(i) + X] = p ? cpack(p[0], p[1]) : czero();
+                }
+            if (!ctx.interior)
+                for (int e = 0; e < F * L; ++e) ols2_col_patch<R2>(smem.data(), e, ctx.s, io.ax);
+            for (int X = 0; X < F; ++X) {
+                float2* sx = smem.data() + X;
+                for (int n2 = 0; n2 < R2; ++n2) ols2_col_pass1<R2>(sx, n2);
+                for (int k1 = 0; k1 < 32; ++k1) { cplx w[R2]; T.item_twiddles<R2>(k1, w); ols2_pass2<R2, F>(sx, k1, w, T.kt.data()); }
+                for (int n2 = 0; n2 < R2; ++n2) {
+                    cplx w[32], x[32];
+                    T.item_twiddles<32>(n2, w);
+                    ols2_col_pass3_load<R2>(sx, n2, x);
+                    ols2_col_pass3_store<R2>(io, ctx, X, n2, x, w);
+                }
+            }
+        }
+    }
+}
+
 static int ols_row_pass(const uint8_t* in_stripe, float* q, const GaussGeometry& gg, const ShardGeom& sg, double sigma,
                         int nranks, float* const* qpeer = nullptr, int rank = 0)
 {
@@ -140,6 +218,7 @@ static int ols_row_pass(const uint8_t* in_stripe, float* q, const GaussGeometry&
     io.srows = sg.stripe_rows; io.qpitch = sg.qpitch; io.cpart = sg.cpart; io.nparts = nranks;
     io.ax = sg.ols_row; io.nunits = io.ax.nblocks * io.npairs;
     if (qpeer) { io.peer = 1; io.rank = rank; for (int p = 0; p < nranks; ++p) io.qpeer[p] = qpeer[p]; }
+    if (io.ax.R2 == 32) { ols2_row_units<32>(io, Ols2Tables(32, sigma, gg.ksize)); return 0; }
     const OlsTables T(io.ax.R0, sigma, gg.ksize);
 #define F_(R) ols_row_units<R>(io, T)
     OLS_R0_SWITCH(io.ax.R0, F_)
@@ -157,11 +236,16 @@ static int ols_col_pass(const float* q_recv, uint8_t* out_cols, const GaussGeome
     if (io.noct <= 0) return 0;
     std::vector<uint8_t> U(static_cast<size_t>(3) * io.noct * rows * 8);
     io.u = U.data(); io.rows = rows; io.ax = sg.ols_col; io.nunits = io.ax.nblocks * 3 * io.noct;
-    const OlsTables T(io.ax.R0, sigma, gg.ksize);
     io.q = q_recv; io.qpitch = sg.qpitch; io.rows_total = nranks * sg.stripe_rows;
+    if (io.ax.R2 == 32) {
+        io.order = 1; io.nbl = io.ax.nblocks; io.nunits = io.nbl * 3 * 2 * ((io.noct + 1) / 2);
+        ols2_col_units<32>(io, Ols2Tables(32, sigma, gg.ksize));
+    } else {
+        const OlsTables T(io.ax.R0, sigma, gg.ksize);
 #define F_(R) ols_col_units<R>(io, T)
-    OLS_R0_SWITCH(io.ax.R0, F_)
+        OLS_R0_SWITCH(io.ax.R0, F_)
 #undef F_
+    }
     for (int r = 0; r < rows; ++r)
         for (int c = 0; c < io.noct * 8 && c < 2 * sg.cpp; ++c)
             for (int ch = 0; ch < 3; ++ch)

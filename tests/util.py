@@ -86,7 +86,7 @@ class Emulator:
         src = os.path.join(HERE, "emul", "emulate.cpp")
         csrc = os.path.join(os.path.dirname(HERE), "blur_algorithms_b200", "csrc")
         deps = [src] + [os.path.join(csrc, f) for f in ("fft_core.cuh", "fft_plan.hpp", "blur_io.cuh", "dft_codelets.cuh", "ols_core.cuh", "ols_plan.hpp",
-                                                           "dft_codelets2.cuh", "cplx2.cuh")]
+                                                           "dft_codelets2.cuh", "cplx2.cuh", "ols2_core.cuh", "dft_codelets3.cuh")]
         if not os.path.exists(so) or any(os.path.getmtime(d) > os.path.getmtime(so) for d in deps if os.path.exists(d)):
             subprocess.run(["g++", "-O2", "-std=c++17", "-fopenmp", "-fPIC", "-shared", "-o", so, src], check=True)
         L = self.lib = C.CDLL(so)
