@@ -20,6 +20,7 @@
 #include "ols_plan.hpp"
 
 namespace blurb200 {
+__attribute__((visibility("hidden"))) void note_launches(uint64_t n);   // counter of this library's own kernel launches (other TUs)
 // boxblur.cu
 cudaError_t launch_box_fused_pass(const uint8_t* in, uint8_t* out, int w, int h, int C, int r, int batch, size_t img_stride,
                                   cudaStream_t st);
@@ -529,6 +530,10 @@ boxblur_v_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int 
 
 }  // namespace
 
+namespace blurb200 {
+void note_launches(uint64_t n) { g_launches += n; }
+}
+
 // ------------------------------------------------------------------ plan
 
 struct AxisTables {
@@ -657,6 +662,9 @@ int build_ols_tables(blur_b200_plan* p, double sigma, int ksize)
     return upload(&p->d_ols_kt_col, kt);
 }
 
+int plan_create_impl(blur_b200_plan* p, const GaussGeometry& gg, int rows, int cols, double sigma, int mode, int device, int rank,
+                     int nranks);
+
 int plan_create(blur_b200_plan** out, int rows, int cols, double sigma, int mode, int device, int rank, int nranks)
 {
     if (!out || rows < 1 || cols < 1 || !(sigma > 0) || (mode != 0 && mode != 1) || nranks < 1 || rank < 0 ||
@@ -668,8 +676,19 @@ int plan_create(blur_b200_plan** out, int rows, int cols, double sigma, int mode
     // (README.md:33-38); deliberate tightening: refuse.
     if (gg.pad < 0 || gg.pad > rows - 1 || gg.pad > cols - 1) return BLUR_B200_EPAD;
     CU_TRY(cudaSetDevice(device));
+    if (const char* e = std::getenv("BLUR_B200_L2_FETCH"))      // experiment knob: L2 fetch granularity in bytes (32 / 64 / 128)
+        CU_TRY(cudaDeviceSetLimit(cudaLimitMaxL2FetchGranularity, static_cast<size_t>(std::atoi(e))));
     blur_b200_plan* p = new (std::nothrow) blur_b200_plan();
     if (!p) return BLUR_B200_ENOMEM;
+    const int rc = plan_create_impl(p, gg, rows, cols, sigma, mode, device, rank, nranks);
+    if (rc != BLUR_B200_OK) { blur_b200_gauss_plan_destroy(p); return rc; }      // nothing leaks on a CUDA failure half way
+    *out = p;
+    return BLUR_B200_OK;
+}
+
+int plan_create_impl(blur_b200_plan* p, const GaussGeometry& gg, int rows, int cols, double sigma, int mode, int device, int rank,
+                     int nranks)
+{
     p->device = device; p->rows = rows; p->cols = cols; p->sigma = sigma; p->mode = mode; p->gg = gg;
     p->rank = rank; p->nranks = nranks;
     const ShardGeom sg = shard_geometry(gg, mode, rank, nranks);
@@ -708,7 +727,7 @@ int plan_create(blur_b200_plan** out, int rows, int cols, double sigma, int mode
         rc = build_axis(p->row, gg.n_row, sigma, gg.ksize, mode);
         if (rc == BLUR_B200_OK) rc = build_axis(p->col, gg.n_col, sigma, gg.ksize, mode);
     }
-    if (rc != BLUR_B200_OK) { blur_b200_gauss_plan_destroy(p); return rc; }
+    if (rc != BLUR_B200_OK) return rc;
     cudaDeviceProp prop;
     CU_TRY(cudaGetDeviceProperties(&prop, device));
     p->num_sms = prop.multiProcessorCount;
@@ -716,7 +735,6 @@ int plan_create(blur_b200_plan** out, int rows, int cols, double sigma, int mode
     CU_TRY(cudaMemset(p->d_q, 0, sizeof(float) * p->block_floats * nranks));   // phantom column of an odd width stays 0
     CU_TRY(cudaMalloc(&p->d_u, static_cast<size_t>(3) * 2 * p->cpp * rows));
     CU_TRY(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
-    *out = p;
     return BLUR_B200_OK;
 }
 
@@ -802,8 +820,7 @@ int run_col_pass_to_u(blur_b200_plan* p, const float* d_q_chunks, cudaStream_t s
         if (blk_end < 0) blk_end = io.ax.nblocks;
         io.b0 = blk_begin;
         io.nbl = blk_end - blk_begin;
-        io.order = io.ax.R2 ? 1 : 0;
-        io.nunits = io.order ? io.nbl * 3 * 2 * cdiv(io.noct, 2) : io.nbl * 3 * io.noct;
+        io.nunits = io.ax.R2 ? io.nbl * 3 * cdiv(io.noct, 2) : io.nbl * 3 * io.noct;
         if (p->quirk_ols) {
             io.corr = p->d_corr_col; io.corr_pitch = p->qpitch;
         }
@@ -883,6 +900,8 @@ int blur_b200_gaussian_window(double sigma, int max_width) { return gaussian_win
 int blur_b200_get_gaussian(float* kernel, double sigma, int width, int fft_length)
 {
     if (!kernel || width < 0 || fft_length < 0) return BLUR_B200_EINVAL;
+    const int eff_width = width ? width : gaussian_window(sigma);
+    if (fft_length && fft_length < eff_width) return BLUR_B200_EINVAL;     // the reference would write past the vector (Source.cpp:80-89)
     std::vector<float> k;
     get_gaussian(k, sigma, width, fft_length);
     std::memcpy(kernel, k.data(), sizeof(float) * k.size());
@@ -971,6 +990,7 @@ int blur_b200_gauss_plan_info(const blur_b200_plan* p, int64_t info[24])
 int blur_b200_gauss_run_device(blur_b200_plan* p, const uint8_t* d_in, uint8_t* d_out, void* stream)
 {
     if (!p || !d_in || !d_out || p->nranks != 1) return BLUR_B200_EINVAL;
+    CU_TRY(cudaSetDevice(p->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     int rc = run_row_pass(p, d_in, p->d_q, st);
     if (rc) return rc;
@@ -1121,6 +1141,7 @@ int blur_b200_gauss_u8c3(uint8_t* h_bgr, int rows, int cols, double sigma, int n
 int blur_b200_gauss_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, float* d_q, void* stream)
 {
     if (!p || !d_in_stripe || !d_q) return BLUR_B200_EINVAL;
+    CU_TRY(cudaSetDevice(p->device));
     return run_row_pass(p, d_in_stripe, d_q, static_cast<cudaStream_t>(stream));
 }
 
@@ -1130,6 +1151,7 @@ int blur_b200_gauss_row_pass_peer(blur_b200_plan* p, const uint8_t* d_in_stripe,
     if (p->algo != 1 || p->quirk_ols) return BLUR_B200_ESIZE;      // only the overlap-save row kernel has the fused epilogue
     for (int k = 0; k < npeers; ++k)
         if (!q_peers[k]) return BLUR_B200_EINVAL;
+    CU_TRY(cudaSetDevice(p->device));
     return run_row_pass(p, d_in_stripe, p->d_q, static_cast<cudaStream_t>(stream), q_peers);
 }
 
@@ -1141,6 +1163,7 @@ int blur_b200_gauss_row_pass_push(blur_b200_plan* p, const uint8_t* d_in_stripe,
     for (int k = 0; k < npeers; ++k)
         if (!q_peers[k]) return BLUR_B200_EINVAL;
     if (p->valid_rows <= 0) return BLUR_B200_OK;
+    CU_TRY(cudaSetDevice(p->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int N = p->nranks, rank = p->rank;
     if (!p->push_stream) {
@@ -1240,6 +1263,7 @@ int blur_b200_gauss_row_pass_push(blur_b200_plan* p, const uint8_t* d_in_stripe,
 int blur_b200_gauss_col_pass(blur_b200_plan* p, const float* d_q_chunks, uint8_t* d_out_cols, void* stream)
 {
     if (!p || !d_q_chunks || !d_out_cols) return BLUR_B200_EINVAL;
+    CU_TRY(cudaSetDevice(p->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     int rc = run_col_pass_to_u(p, d_q_chunks, st);
     if (rc) return rc;
@@ -1249,6 +1273,7 @@ int blur_b200_gauss_col_pass(blur_b200_plan* p, const float* d_q_chunks, uint8_t
 int blur_b200_gauss_rowpass_f32(blur_b200_plan* p, const uint8_t* d_in, float* d_planar, void* stream)
 {
     if (!p || !d_in || !d_planar || p->nranks != 1) return BLUR_B200_EINVAL;
+    CU_TRY(cudaSetDevice(p->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     int rc = run_row_pass(p, d_in, p->d_q, st);
     if (rc) return rc;
@@ -1281,11 +1306,8 @@ int blur_b200_fastboxblur_device(uint8_t* d_img, int w, int h, int channels, int
     const size_t img_bytes = static_cast<size_t>(w) * h * channels;
     const size_t smem_h = static_cast<size_t>(w + 2 * r) * channels * sizeof(uint32_t);
     if (smem_h > 200 * 1024) return BLUR_B200_ESIZE;
-    static size_t configured = 0;
-    if (smem_h > 48 * 1024 && smem_h > configured) {
+    if (smem_h > 48 * 1024)     // per-device function attribute: set on every call, never cached process-wide
         CU_TRY(cudaFuncSetAttribute(boxblur_h_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem_h)));
-        configured = smem_h;
-    }
     // Fused path: one kernel per 2-D pass over the whole batch, ping-pong between image and scratch.
     if (!std::getenv("BLUR_B200_BOX_UNFUSED")) {
         uint8_t *src = d_img, *dst = d_scratch;
@@ -1518,6 +1540,5 @@ int blur_b200_flip_block_f32_host(const float* h_in, float* h_out, int w, int h)
 }
 
 uint64_t blur_b200_kernel_launches(void) { return g_launches.load(); }
-void blur_b200_count_launches(uint64_t n) { g_launches += n; }
 
 }  // extern "C"

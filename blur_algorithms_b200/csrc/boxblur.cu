@@ -163,11 +163,10 @@ boxblur_tile_kernel(const __grid_constant__ BoxTileArgs a)
 template <int C>
 cudaError_t launch_tile(const BoxTileArgs& a, int tiles, int batch, size_t smem, cudaStream_t st)
 {
-    static size_t configured = 0;
-    if (smem > configured) {
+    // per-device function attribute: set on every launch (cheap), never cached process-wide
+    if (smem > 48 * 1024) {
         cudaError_t e = cudaFuncSetAttribute(boxblur_tile_kernel<C>, cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
         if (e != cudaSuccess) return e;
-        configured = smem;
     }
     boxblur_tile_kernel<C><<<dim3(tiles, batch), kBoxThreads, smem, st>>>(a);
     return cudaGetLastError();

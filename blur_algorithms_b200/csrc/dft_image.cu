@@ -20,6 +20,7 @@
 #include "fft_dispatch.cuh"
 #include "fft_plan.hpp"
 
+namespace blurb200 { __attribute__((visibility("hidden"))) void note_launches(uint64_t n); }   // blur_b200.cu: internal launch counter
 using namespace blurb200;
 
 namespace {
@@ -326,7 +327,6 @@ int threads_for(int n32) { return std::max(128, std::min(kMaxThreads, ((n32 + 31
 
 extern "C" {
 
-void blur_b200_count_launches(uint64_t n);   // blur_b200.cu
 
 int blur_b200_dft_image_sizes(int rows, int cols, double nsmooth, int padded[2], int border[4])
 {
@@ -387,9 +387,9 @@ int blur_b200_dft_image_device(const uint8_t* d_in, uint8_t* d_out, int rows, in
         spec_finish_kernel<<<dim3((cols + 31) / 32, (rows + 31) / 32), dim3(32, 8), 0, st>>>(g_ws.Tq, d_out, gm.H, gm.W, WC, rows, cols,
                                                                                         gm.border[0], gm.border[2]);
         CU_TRY(cudaGetLastError());
-        blur_b200_count_launches(1);
+        blurb200::note_launches(1);
     }
-    blur_b200_count_launches(2);
+    blurb200::note_launches(2);
     CU_TRY(cudaStreamSynchronize(st));      // the shared workspace is free again when the call returns
     return BLUR_B200_OK;
 }

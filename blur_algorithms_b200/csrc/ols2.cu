@@ -21,13 +21,17 @@ cudaError_t launch_ols2_row(const OlsRowIO& io, const float2* tw2, const float* 
     if (io.ax.R2 != 32) return cudaErrorInvalidValue;
     constexpr int R2 = 32;
     constexpr int smem = ols2_row_smem_bytes<R2>();
-    cudaError_t e = opt_in_smem(ols2_row_kernel<R2>, smem);
+    const bool sharded = io.nparts > 1;
+    cudaError_t e = sharded ? opt_in_smem(ols2_row_kernel<R2, true>, smem) : opt_in_smem(ols2_row_kernel<R2, false>, smem);
     if (e != cudaSuccess) return e;
     static const int ctas_env = std::getenv("BLUR_B200_ROW_CTAS") ? std::atoi(std::getenv("BLUR_B200_ROW_CTAS")) : 0;
     const int per_sm = ctas_env > 0 ? std::min(ctas_env, BLUR_OLS2_ROW_CTAS) : BLUR_OLS2_ROW_CTAS;
     const int grid = std::min((io.nunits + kOls2RowWarps - 1) / kOls2RowWarps, num_sms * per_sm);
     if (grid <= 0) return cudaSuccess;
-    ols2_row_kernel<R2><<<grid, 32 * kOls2RowWarps, smem, stream>>>(io, tw2, kt);
+    if (sharded)
+        ols2_row_kernel<R2, true><<<grid, 32 * kOls2RowWarps, smem, stream>>>(io, tw2, kt);
+    else
+        ols2_row_kernel<R2, false><<<grid, 32 * kOls2RowWarps, smem, stream>>>(io, tw2, kt);
     return cudaGetLastError();
 }
 
@@ -43,7 +47,7 @@ cudaError_t launch_ols2_col(const OlsColIO& io_in, const float* d_q, int qpitch,
     if (e != cudaSuccess) return e;
     static const int ctas_env = std::getenv("BLUR_B200_COL_CTAS") ? std::atoi(std::getenv("BLUR_B200_COL_CTAS")) : 0;
     const int per_sm = ctas_env > 0 ? std::min(ctas_env, BLUR_OLS2_COL_CTAS) : BLUR_OLS2_COL_CTAS;
-    const int grid = std::min(io.nunits, num_sms * per_sm);
+    const int grid = std::min(io.nunits, num_sms * per_sm);       // nunits = (strip, block) pairs, dealt out in contiguous runs
     if (grid <= 0) return cudaSuccess;
     ols2_col_kernel<R2><<<grid, 128, smem, stream>>>(io, tw2, kt);
     return cudaGetLastError();

@@ -50,6 +50,17 @@ BLUR_HD void ols2_item_range(int t, int halo, int nvalid, int& jlo, int& jhi)
     jhi = b < 0 ? -1 : b / R2;
 }
 
+// the same as a bit mask: bit j set <=> output j of item t is kept
+template <int R2>
+BLUR_HD uint32_t ols2_item_mask(int t, int halo, int nvalid)
+{
+    int jlo, jhi;
+    ols2_item_range<R2>(t, halo, nvalid, jlo, jhi);
+    if (jhi < jlo) return 0u;
+    if (jhi > 31) jhi = 31;
+    return ((2u << jhi) - 1u) & ~((1u << jlo) - 1u);
+}
+
 // ---- pass 2 (both kernels): item k1 of transform X; sx = tile base + X
 template <int R2, int F>
 BLUR_HD void ols2_pass2(cplx* __restrict__ sx, int k1, const cplx* __restrict__ w, const float* __restrict__ kt)
@@ -75,28 +86,40 @@ BLUR_HD void ols2_row_pass1(cplx* __restrict__ tile, const OlsRowIO::Ctx& c, int
     cplx x[kOls2R1];
     const uint8_t* pa = c.raw + c.ia + 3 * n2 + ch;
     const int db = c.ib - c.ia;
-    if (c.has_b) {
 #ifdef __CUDA_ARCH__
-        const cplx bias = cpack(8388608.f, 8388608.f);
+    // uint8 -> float without the conversion pipe and without a subtraction per element: one PRMT
+    // drops the byte into bits 8..15 of 0x47000000, i.e. the float 32768 + b.  The DFT sees
+    // b + 32768; every butterfly of the radix-32 codelet only adds or subtracts bias-carrying
+    // values with each other before any multiplication, all of them integers below 2^21, so the
+    // arithmetic is exact: the bias cancels in every difference and arrives as 32 * 32768 = 2^20
+    // in output 0, where ONE subtraction per item removes it.
+    if (c.has_b) {
 #pragma unroll
         for (int j = 0; j < kOls2R1; ++j)
-            x[j] = csub(cpack(__uint_as_float(0x4B000000u | pa[3 * R2 * j]), __uint_as_float(0x4B000000u | pa[db + 3 * R2 * j])), bias);
-#else
-#pragma unroll
-        for (int j = 0; j < kOls2R1; ++j) x[j] = cpack(OlsRowIO::u8f(pa[3 * R2 * j]), OlsRowIO::u8f(pa[db + 3 * R2 * j]));
-#endif
+            x[j] = cpack(__uint_as_float(__byte_perm(pa[3 * R2 * j], 0x47000000u, 0x7604)),
+                         __uint_as_float(__byte_perm(pa[db + 3 * R2 * j], 0x47000000u, 0x7604)));
     } else {
 #pragma unroll
+        for (int j = 0; j < kOls2R1; ++j) x[j] = cpack(__uint_as_float(__byte_perm(pa[3 * R2 * j], 0x47000000u, 0x7604)), 0.f);
+    }
+    CDftV<kOls2R1>::fwd(x);
+    x[0] = csub(x[0], cpack(1048576.f, c.has_b ? 1048576.f : 0.f));
+#else
+    if (c.has_b) {
+        for (int j = 0; j < kOls2R1; ++j) x[j] = cpack(OlsRowIO::u8f(pa[3 * R2 * j]), OlsRowIO::u8f(pa[db + 3 * R2 * j]));
+    } else {
         for (int j = 0; j < kOls2R1; ++j) x[j] = cpack(OlsRowIO::u8f(pa[3 * R2 * j]), 0.f);
     }
     CDftV<kOls2R1>::fwd(x);
+#endif
     cplx* col = tile + n2;
 #pragma unroll
     for (int k = 0; k < kOls2R1; ++k) col[(R2 + 1) * k] = x[k];
 }
 
 // pass 3: item n2 -> Q.  Output j of the item is image column s + R2 j + n2 of lines (ra, ra+1).
-template <int R2>
+// SHARDED = false: single part (nparts == 1), the only epilogue the single-GPU kernel carries.
+template <int R2, bool SHARDED>
 BLUR_HD void ols2_row_pass3(const cplx* __restrict__ tile, const OlsRowIO& io, const OlsRowIO::Ctx& c, int ch, int n2,
                             const cplx* __restrict__ w)
 {
@@ -112,21 +135,20 @@ BLUR_HD void ols2_row_pass3(const cplx* __restrict__ tile, const OlsRowIO& io, c
 #pragma unroll
         for (int j = 0; j < kOls2R1; ++j) x[j] = cadd(x[j], cc);
     }
-    int jlo, jhi;
-    ols2_item_range<R2>(n2, io.ax.halo, c.nvalid, jlo, jhi);
+    const uint32_t keep = ols2_item_mask<R2>(n2, io.ax.halo, c.nvalid);
     const int x0 = c.s + n2;
-    const int nparts = io.nparts, qpitch = io.qpitch;
+    const int nparts = SHARDED ? io.nparts : 1, qpitch = io.qpitch;
     float* qc = c.qa + static_cast<size_t>(ch) * nparts * io.srows * qpitch;
-    if (nparts == 1) {
+    if (!SHARDED) {
         float* d = qc + x0;
+#pragma unroll
+        for (int j = 0; j < kOls2R1; ++j)
+            if (keep >> j & 1u) d[R2 * j] = cre(x[j]);
         if (c.has_b) {
+            d += qpitch;
 #pragma unroll
             for (int j = 0; j < kOls2R1; ++j)
-                if (j >= jlo && j <= jhi) { d[R2 * j] = cre(x[j]); d[qpitch + R2 * j] = cim(x[j]); }
-        } else {
-#pragma unroll
-            for (int j = 0; j < kOls2R1; ++j)
-                if (j >= jlo && j <= jhi) d[R2 * j] = cre(x[j]);
+                if (keep >> j & 1u) d[R2 * j] = cim(x[j]);
         }
     } else if (io.ax.V <= 2 * io.cpart) {
         // the block's outputs span at most three parts: three base pointers, then a select per element
@@ -141,7 +163,7 @@ BLUR_HD void ols2_row_pass3(const cplx* __restrict__ tile, const OlsRowIO& io, c
         const int e1 = c.b1 - x0, e2 = e1 + io.cpart;
 #pragma unroll
         for (int j = 0; j < kOls2R1; ++j) {
-            const bool va = j >= jlo && j <= jhi, vb = va && c.has_b;
+            const bool va = keep >> j & 1u, vb = va && c.has_b;
             float* d = R2 * j >= e2 ? pp[2] : (R2 * j >= e1 ? pp[1] : pp[0]);
             if (va) d[R2 * j] = cre(x[j]);
             if (vb) d[qpitch + R2 * j] = cim(x[j]);
@@ -149,7 +171,7 @@ BLUR_HD void ols2_row_pass3(const cplx* __restrict__ tile, const OlsRowIO& io, c
     } else {
 #pragma unroll
         for (int j = 0; j < kOls2R1; ++j) {
-            const bool va = j >= jlo && j <= jhi, vb = va && c.has_b;
+            const bool va = keep >> j & 1u, vb = va && c.has_b;
             const int xx = va ? x0 + R2 * j : 0;
             const int part = xx / io.cpart;
             float* d = io.peer ? io.qpeer[part] + (static_cast<size_t>(ch * nparts + io.rank) * io.srows + c.ra) * qpitch + (xx - part * io.cpart)
@@ -158,6 +180,26 @@ BLUR_HD void ols2_row_pass3(const cplx* __restrict__ tile, const OlsRowIO& io, c
             if (vb) d[qpitch] = cim(x[j]);
         }
     }
+}
+
+// (uint8_t)(v + 0.5f) of both halves (Utils.hpp:189,204-206: float add, then truncation).  The blur of
+// non-negative data with non-negative taps is >= -rounding noise, so v + 0.5f > 0 and truncation
+// = floor, which one packed add in round-down mode delivers in the low mantissa byte of
+// 2^23 + t: no float->int conversion instruction (those run on the quarter-rate XU pipe).
+// CLAMP (pffft-quirk plans: the Nyquist correction can drive values below -0.5): negatives -> 0, the
+// saturation OlsColIO::to_u8x2 documents.
+template <bool CLAMP>
+BLUR_HD uint32_t ols2_to_u8x2(cplx v)
+{
+#ifdef __CUDA_ARCH__
+    cplx t = cadd(v, cpack(0.5f, 0.5f));
+    if (CLAMP) t = cpack(fmaxf(cre(t), 0.f), fmaxf(cim(t), 0.f));
+    const cplx m = cpack(8388608.f, 8388608.f);
+    asm("add.rm.f32x2 %0, %1, %2;" : "=l"(t) : "l"(t), "l"(m));
+    return __byte_perm(__float_as_uint(cre(t)), __float_as_uint(cim(t)), 0x0040);
+#else
+    return OlsColIO::to_u8x2(v);
+#endif
 }
 
 // ---- column pass ------------------------------------------------------------------------------
@@ -197,12 +239,39 @@ BLUR_HD void ols2_col_pass3_store(const OlsColIO& io, const OlsColIO::Ctx& c, in
 #pragma unroll
         for (int j = 0; j < kOls2R1; ++j) x[j] = cadd(x[j], cc);
     }
-    int jlo, jhi;
-    ols2_item_range<R2>(n2, io.ax.halo, c.nvalid, jlo, jhi);
+    const uint32_t keep = ols2_item_mask<R2>(n2, io.ax.halo, c.nvalid);
     uint16_t* d = reinterpret_cast<uint16_t*>(c.ua + (static_cast<ptrdiff_t>(c.s + n2) * 8 + 2 * X));
+    if (io.corr) {
 #pragma unroll
-    for (int j = 0; j < kOls2R1; ++j)
-        if (j >= jlo && j <= jhi) d[4 * R2 * j] = static_cast<uint16_t>(OlsColIO::to_u8x2(x[j]));
+        for (int j = 0; j < kOls2R1; ++j)
+            if (keep >> j & 1u) d[4 * R2 * j] = static_cast<uint16_t>(ols2_to_u8x2<true>(x[j]));
+    } else {
+#pragma unroll
+        for (int j = 0; j < kOls2R1; ++j)
+            if (keep >> j & 1u) d[4 * R2 * j] = static_cast<uint16_t>(ols2_to_u8x2<false>(x[j]));
+    }
+}
+
+struct Ols2ColWalk {
+    int strip, b;        // current pair
+    BLUR_HD void next(int nbl) { if (++b == nbl) { b = 0; ++strip; } }
+};
+
+// sub-unit context of (strip, b, member m): channel = strip % 3, octet = 2 * (strip / 3) + m
+BLUR_HD OlsColIO::Ctx ols2_col_ctx(const OlsColIO& io, int strip, int b, int m)
+{
+    OlsColIO::Ctx c;
+    c.ch = strip % 3;
+    c.oct = 2 * (strip / 3) + m;
+    c.valid = c.oct < io.noct;
+    if (!c.valid) c.oct = io.noct - 1;
+    const int blk = io.b0 + b;
+    c.ua = io.u + (static_cast<size_t>(c.ch) * io.noct + c.oct) * io.rows * 8;
+    c.qa = io.q + static_cast<size_t>(c.ch) * io.rows_total * io.qpitch + c.oct * 8;
+    c.s = blk * io.ax.V - io.ax.halo;
+    c.nvalid = io.rows - blk * io.ax.V < io.ax.V ? io.rows - blk * io.ax.V : io.ax.V;
+    c.interior = c.s >= 0 && c.s + io.ax.L <= io.rows;
+    return c;
 }
 
 // Patch entry e = 4*i + X of an edge block (rows outside the image take their reflect-101 source,

@@ -8,12 +8,10 @@ template <int R0>
 static cudaError_t launch_col(const OlsColIO& io, const float2* twA, const float2* twB, const float* kt, int num_sms,
                               cudaStream_t stream)
 {
-    static bool configured = false;
     constexpr int smem = ols_smem_bytes<R0, 4>();
-    if (!configured) {
+    {   // per-device function attribute: set on every launch (cheap), never cached process-wide
         cudaError_t e = cudaFuncSetAttribute(ols_col_kernel<R0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
-        configured = true;
     }
     const int grid = std::min(io.nunits, num_sms * ols_ctas_per_sm<R0, 4>());
     if (grid <= 0) return cudaSuccess;

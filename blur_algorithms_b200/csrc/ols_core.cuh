@@ -264,10 +264,10 @@ struct OlsRowIO {
         st.dst = st.b0 + lead - off;                   // multiple of 16 by construction
         return st;
     }
-    BLUR_HD Ctx begin(int unit, uint8_t* raw, int raw_pitch) const
+    BLUR_HD Ctx begin(int unit, uint8_t* raw, int raw_pitch) const { return begin(unit % npairs, unit / npairs, raw, raw_pitch); }
+    BLUR_HD Ctx begin(int pair, int b, uint8_t* raw, int raw_pitch) const
     {
         Ctx c;
-        const int pair = unit % npairs, b = unit / npairs;
         c.raw = raw;
         c.ra = 2 * pair;
         c.has_b = c.ra + 1 < rows;
@@ -416,12 +416,7 @@ struct OlsColIO {
     int nunits;
     OlsAxis ax;            // len = rows
     int b0;                // first block of this launch (the streamed host path launches block by block)
-    int nbl;               // order 1: blocks in this launch
-    int order;             // unit order.  0: octet fastest, then channel, then block (nunits = nbl*3*noct)
-                           // 1: member of an octet pair fastest, then block, then channel, then octet pair
-                           //    (nunits = nbl*3*2*ceil(noct/2)): the two halves of every 64-byte run of a Q row
-                           //    and the halo rows shared by vertically adjacent blocks are fetched at about the
-                           //    same time by neighbouring CTAs, so each reaches DRAM once
+    int nbl;               // blocks in this launch (two-factor kernel: nunits = nbl * 3 * ceil(noct / 2) strip-block pairs)
     const float* corr;     // pffft Nyquist quirk, see OlsRowIO::corr: corr[ch * corr_pitch + column]
     int corr_pitch;
 
@@ -436,21 +431,11 @@ struct OlsColIO {
     BLUR_HD Ctx begin(int unit) const
     {
         Ctx c;
-        int b;
-        if (order == 0) {
-            c.oct = unit % noct;
-            const int rest = unit / noct;
-            c.ch = rest % 3;
-            b = b0 + rest / 3;
-        } else {
-            const int u2 = unit >> 1;
-            b = b0 + u2 % nbl;
-            const int rest = u2 / nbl;
-            c.ch = rest % 3;
-            c.oct = 2 * (rest / 3) + (unit & 1);
-        }
-        c.valid = c.oct < noct;
-        if (!c.valid) c.oct = noct - 1;
+        c.oct = unit % noct;
+        const int rest = unit / noct;
+        c.ch = rest % 3;
+        const int b = b0 + rest / 3;
+        c.valid = true;
         c.ua = u + (static_cast<size_t>(c.ch) * noct + c.oct) * rows * 8;
         c.qa = q + static_cast<size_t>(c.ch) * rows_total * qpitch + c.oct * 8;
         c.s = b * ax.V - ax.halo;

@@ -233,7 +233,8 @@ ols_col_kernel(const __grid_constant__ OlsColIO io, const float2* __restrict__ t
 #pragma unroll 1
             for (int t = sub; t < 256; t += kOlsThreads) {
                 ols_pass_a_inv<R0, F>(sx, X, t, t + kOlsThreads, twA, w, io, ctx);
-                ols_col_fetch<R0>(io, cn, sx, X, t);       // same slots, same thread: no barrier needed
+                __syncwarp();                              // the odd neighbour lane has read the slots its even lane refills
+                ols_col_fetch<R0>(io, cn, sx, X, t);       // same slots, same lane pair: no block barrier needed
             }
         } else {
 #pragma unroll 1

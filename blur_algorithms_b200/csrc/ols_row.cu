@@ -10,12 +10,10 @@ template <int R0>
 static cudaError_t launch_row(const OlsRowIO& io, const float2* twA, const float2* twB, const float* kt, int num_sms,
                               cudaStream_t stream)
 {
-    static bool configured = false;
     constexpr int smem = ols_row_smem_bytes<R0>();
-    if (!configured) {
+    {   // per-device function attribute: set on every launch (cheap), never cached process-wide
         cudaError_t e = cudaFuncSetAttribute(ols_row_kernel<R0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) return e;
-        configured = true;
     }
     // experiment knob: fewer resident CTAs and a smaller shared-memory carveout leave the twiddle
     // tables room in L1 (BLUR_B200_ROW_CTAS=4 BLUR_B200_ROW_CARVEOUT=86)

@@ -3,13 +3,21 @@
 Row pass on row stripes, one exchange of the float32 intermediate (the distributed form of the
 reference's flip_block, Source.cpp:540), column pass on column stripes.  One process per GPU.
 
-On GPUs the exchange is FUSED into the row-pass kernel: every rank's receive buffer lives in
-symmetric memory (torch.distributed._symmetric_memory: CUDA peer mappings over NVLink/NVSwitch),
-and the kernel's epilogue stores each result directly into the buffer of the rank that owns its
-column (blur_b200_gauss_row_pass_peer).  The transfer overlaps the FFTs block by block; no staging
-copy in HBM, no collective on the data path — two device-side barriers per blur order the ranks.
-Fallback (`fused=False`, or symmetric memory unavailable): a local Q buffer + NCCL all_to_all.
-The CPU tests run the same host logic over gloo with the two passes supplied as callables.
+On GPUs every rank's receive buffer lives in symmetric memory (torch.distributed._symmetric_memory:
+CUDA peer mappings over NVLink/NVSwitch) and no collective library call is on the data path.  Two
+exchange modes (BLUR_B200_EXCHANGE):
+  "push"  (default) the row pass runs in wave-aligned chunks of row pairs; the kernel writes this
+          rank's own part into its receive buffer and the rest into a local send buffer, and as soon
+          as a chunk is done the GPU's COPY ENGINES move it into the owners' buffers (one 2-D peer
+          copy per destination) underneath the next chunk's FFTs (blur_b200_gauss_row_pass_push);
+  "store" the row kernel's epilogue stores every result straight into the owner's buffer
+          (blur_b200_gauss_row_pass_peer): no staging, but 4-byte remote stores.
+Two device-side barriers per blur order the ranks.  Fallback (`fused=False`, or symmetric memory
+unavailable): a local Q buffer + NCCL all_to_all.  The CPU tests run the same host logic over gloo
+with the two passes supplied as callables.
+
+Batches of images (BASELINE config 5, batched Gaussian) do not need any of this: ShardedBatch deals
+image i to rank i mod P and every rank runs the single-GPU entry points on its share.
 
 Layout contract (blur_b200_gauss_shard_geometry in include/blur_b200.h):
     algorithm 0 (full-length FFT per line)   q_send [nranks][3][cpp][stripe_rows][2]
@@ -83,6 +91,63 @@ def _all_to_all(send: torch.Tensor, recv: torch.Tensor, n: int, group) -> None:
             q.wait()
 
 
+class ShardedBatch:
+    """A batch of independent images over the ranks: image i belongs to rank i mod nranks (SURVEY.md
+    §8e row 2; BASELINE config 5).  No exchange, no collective: every rank calls the single-GPU entry
+    points (fastboxblur_device / fastboxblur_batch, GaussPlan.run / run_host_batch) on its share.
+    Host-side bookkeeping only, so it runs without a GPU (world-size-2 gloo test)."""
+
+    def __init__(self, batch: int, rank: int | None = None, nranks: int | None = None, group=None):
+        if rank is None:
+            rank = dist.get_rank(group) if dist.is_initialized() else 0
+        if nranks is None:
+            nranks = dist.get_world_size(group) if dist.is_initialized() else 1
+        if batch < 0 or nranks < 1 or not 0 <= rank < nranks:
+            raise ValueError("bad batch / rank / nranks")
+        self.batch, self.rank, self.nranks = batch, rank, nranks
+        self.indices = list(range(rank, batch, nranks))
+
+    def __len__(self) -> int:
+        return len(self.indices)
+
+    def take(self, images):
+        """this rank's share of `images` (anything indexable by image number; arrays are gathered)"""
+        if hasattr(images, "shape"):
+            return images[self.rank::self.nranks]
+        return [images[i] for i in self.indices]
+
+    def fastboxblur(self, h_images, ksize: int, passes: int):
+        """Box-blur this rank's share of a host batch [batch, h, w, C] in place through the streamed
+        C-ABI host entry (blur_b200_fastboxblur_batch_host); returns the share (a copy if strided)."""
+        import numpy as np
+        from .api import fastboxblur_batch
+        mine = np.ascontiguousarray(self.take(h_images))
+        if len(mine):
+            fastboxblur_batch(mine, ksize, passes)
+        return mine
+
+    def gauss(self, plan, h_images):
+        """Gaussian-blur this rank's share of a list of host images in place through
+        GaussPlan.run_host_batch (streamed uploads / kernels / downloads)."""
+        mine = self.take(h_images)
+        if len(mine):
+            plan.run_host_batch(list(mine))
+        return mine
+
+    def gather(self, mine, group=None):
+        """All ranks' shares back in image order (a list of length batch), via all_gather_object —
+        convenience for tests and small batches; production callers keep results sharded."""
+        if self.nranks == 1 or not dist.is_initialized():
+            return list(mine)
+        parts = [None] * self.nranks
+        dist.all_gather_object(parts, list(mine), group=group)
+        out = [None] * self.batch
+        for r, p in enumerate(parts):
+            for j, item in enumerate(p):
+                out[r + j * self.nranks] = item
+        return out
+
+
 class ShardedGaussBlur:
     """One rank's half of the sharded blur.  `row_pass(in_stripe, q_send)` and
     `col_pass(q_recv, out_cols)` default to the CUDA plan; tests may inject CPU stand-ins."""
@@ -134,6 +199,27 @@ class ShardedGaussBlur:
     def fused(self) -> bool:
         return self.symm is not None
 
+    def describe_exchange(self) -> str:
+        """What moves the float32 intermediate between the ranks (for bench.py's config line)."""
+        if not self.fused:
+            return "NCCL all_to_all of the float32 intermediate (local send buffer)"
+        if self.exchange_mode == "store":
+            return "row-kernel epilogue stores into the owners' symmetric-memory buffers over NVLink (4-byte peer stores)"
+        return (f"row pass in {self.nchunks} wave-aligned chunks; copy engines (cudaMemcpy2DAsync peer copies, one per "
+                "destination and chunk) move each finished chunk from a local send buffer into the owners' "
+                "symmetric-memory buffers under the next chunk's FFTs")
+
+    def row_pass_only(self) -> None:
+        """The row phase as run() issues it, without the two barriers (per-pass timing in bench.py)."""
+        if self.geom.valid_rows <= 0:
+            return
+        if not self.fused:
+            self._row_pass(self._last_in, self.q_send)
+        elif self.exchange_mode == "store":
+            self.plan.row_pass_peer(self._last_in, self.peer_ptrs)
+        else:
+            self.plan.row_pass_push(self._last_in, self.peer_ptrs, self.nchunks)
+
     def run(self, in_stripe: torch.Tensor) -> torch.Tensor:
         """in_stripe: uint8 [valid_rows, cols, 3] (this rank's rows).  Returns this rank's column
         stripe of the result, uint8 [rows, valid_cols, 3] (a view into an internal buffer)."""
@@ -142,6 +228,7 @@ class ShardedGaussBlur:
 
     def _rows(self, in_stripe: torch.Tensor) -> None:
         """row pass of this rank's stripe + the exchange (the distributed flip_block, Source.cpp:540)"""
+        self._last_in = in_stripe
         if self.symm is not None:
             # peers may still be reading their buffers (previous blur's column pass)
             self.symm.barrier(channel=0)

@@ -74,6 +74,7 @@ int orc_dft_image(const uint8_t *bgr, uint8_t *out_u8, int rows, int cols, doubl
 int orc_fastboxblur(uint8_t *img, int w, int h, int channels, int ksize, int passes);
 
 int orc_num_threads(void);
+void orc_set_num_threads(int n);
 
 #ifdef __cplusplus
 }

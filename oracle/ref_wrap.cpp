@@ -75,6 +75,16 @@ int ref_has_dft_image(void)
 #endif
 }
 
+/* bench.py --impl reference sets this itself: torchrun exports OMP_NUM_THREADS=1 */
+void ref_set_num_threads(int n)
+{
+#ifdef OMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int ref_num_threads(void)
 {
 #ifdef OMP

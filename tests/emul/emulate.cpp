@@ -169,7 +169,7 @@ static void ols2_row_units(const OlsRowIO& io, const Ols2Tables& T)
                 std::fill(tile.begin(), tile.end(), make_float2(-777.f, 777.f));
                 for (int n2 = 0; n2 < R2; ++n2) ols2_row_pass1<R2>(tile.data(), ctx, ch, n2);
                 for (int k1 = 0; k1 < 32; ++k1) { cplx w[R2]; T.item_twiddles<R2>(k1, w); ols2_pass2<R2, 1>(tile.data(), k1, w, T.kt.data()); }
-                for (int n2 = 0; n2 < R2; ++n2) { cplx w[32]; T.item_twiddles<32>(n2, w); ols2_row_pass3<R2>(tile.data(), io, ctx, ch, n2, w); }
+                for (int n2 = 0; n2 < R2; ++n2) { cplx w[32]; T.item_twiddles<32>(n2, w); if (io.nparts > 1) ols2_row_pass3<R2, true>(tile.data(), io, ctx, ch, n2, w); else ols2_row_pass3<R2, false>(tile.data(), io, ctx, ch, n2, w); }
             }
         }
     }
@@ -183,8 +183,10 @@ static void ols2_col_units(const OlsColIO& io, const Ols2Tables& T)
     {
         std::vector<float2> smem(static_cast<size_t>(F) * ols2_tile_slots<R2>());
 #pragma omp for schedule(dynamic, 4)
-        for (int unit = 0; unit < io.nunits; ++unit) {
-            const OlsColIO::Ctx ctx = io.begin(unit);
+        for (int unit = 0; unit < 2 * io.nunits; ++unit) {
+            // sub-unit = member m of the (strip, block) pair q, as ols2_col_kernel walks them
+            const int q = unit >> 1, m = unit & 1;
+            const OlsColIO::Ctx ctx = ols2_col_ctx(io, q / io.nbl, q % io.nbl, m);
             if (!ctx.valid) continue;
             std::fill(smem.begin(), smem.end(), make_float2(-777.f, 777.f));
             for (int i = 0; i < L; ++i)
@@ -238,7 +240,7 @@ static int ols_col_pass(const float* q_recv, uint8_t* out_cols, const GaussGeome
     io.u = U.data(); io.rows = rows; io.ax = sg.ols_col; io.nunits = io.ax.nblocks * 3 * io.noct;
     io.q = q_recv; io.qpitch = sg.qpitch; io.rows_total = nranks * sg.stripe_rows;
     if (io.ax.R2 == 32) {
-        io.order = 1; io.nbl = io.ax.nblocks; io.nunits = io.nbl * 3 * 2 * ((io.noct + 1) / 2);
+        io.nbl = io.ax.nblocks; io.nunits = io.nbl * 3 * ((io.noct + 1) / 2);
         ols2_col_units<32>(io, Ols2Tables(32, sigma, gg.ksize));
     } else {
         const OlsTables T(io.ax.R0, sigma, gg.ksize);

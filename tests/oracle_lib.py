@@ -64,6 +64,7 @@ class Oracle:
         L.orc_fastboxblur.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int]
         L.orc_fastboxblur.restype = C.c_int
         L.orc_num_threads.restype = C.c_int
+        L.orc_set_num_threads.argtypes = [C.c_int]
 
     # --- sizing / taps
     def gaussian_window(self, sigma: float, max_width: int = 0) -> int:
@@ -180,6 +181,9 @@ class Oracle:
     def num_threads(self) -> int:
         return self.lib.orc_num_threads()
 
+    def set_num_threads(self, n: int) -> None:
+        self.lib.orc_set_num_threads(int(n))
+
 
 class Reference:
     """oracle/_ref/libblurref(.so|_dft.so): the reference's Source.cpp + Utils.hpp compiled
@@ -204,6 +208,7 @@ class Reference:
         L.ref_test.argtypes = [_u8p, C.c_int, C.c_int, C.c_int, C.c_double]
         L.ref_has_dft_image.restype = C.c_int
         L.ref_num_threads.restype = C.c_int
+        L.ref_set_num_threads.argtypes = [C.c_int]
 
     @staticmethod
     def available(dft_image: bool = False) -> bool:
@@ -257,3 +262,7 @@ class Reference:
 
     def num_threads(self) -> int:
         return self.lib.ref_num_threads()
+
+    def set_num_threads(self, n: int) -> None:
+        """OpenMP threads of the reference build (torchrun exports OMP_NUM_THREADS=1)."""
+        self.lib.ref_set_num_threads(int(n))

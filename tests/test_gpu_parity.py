@@ -76,6 +76,105 @@ def test_gauss_golden_reference_outputs(bb):
             assert lsb(out, gold[key + suffix]) <= 1, key + suffix
 
 
+def test_gauss_reference_goldens_1080p_4k(bb):
+    """BASELINE configs 1 and 2 against outputs of the REFERENCE ITSELF (oracle/_ref, committed as
+    tests/golden/reference_large.npz by make_golden_large.py): +-1 LSB on the sampled lattice."""
+    from util import LARGE_GOLDEN_CASES, large_golden, lattice
+    gold = large_golden()
+    for rows, cols, sigma in LARGE_GOLDEN_CASES:
+        img = synth("noise", rows, cols, 0)
+        for fn, name in ((bb.pocketfft_1D, "pocketfft1d"), (bb.pffft_, "pffft")):
+            out = img.copy()
+            fn(out, sigma)
+            want = gold[f"noise_{rows}x{cols}_s{sigma}_{name}_lattice"]
+            got = lattice(out)
+            d = np.abs(got.astype(int) - want.astype(int))
+            assert d.max() <= 1, (rows, cols, name)
+            assert (d > 0).mean() < 2e-3, (rows, cols, name, float((d > 0).mean()))
+
+
+def _cpu_reference_blur(oracle, img, sigma, mode):
+    """oracle/_ref (the reference's own code) when it travelled to this box, else the C restatement."""
+    from oracle_lib import Reference
+    if Reference.available():
+        ref = Reference()
+        ref.set_num_threads(os.cpu_count() or 1)
+        return ref.test(img, 5 if mode == 0 else 3, sigma), "oracle/_ref"
+    oracle.set_num_threads(os.cpu_count() or 1)
+    return oracle.gauss_blur_1d(img, sigma, mode), "liboracle"
+
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_gauss_c3_full_image_every_pixel(bb, oracle, torch, mode, capfd):
+    """BASELINE config 3 in full: the 16384 x 16384 sigma = 50 default_rng(0) image, EVERY pixel
+    against the CPU reference path (pocketfft_1D for the exact mode, pffft_ for the quirk mode),
+    +-1 LSB, mismatching fraction reported."""
+    rows = cols = 16384
+    img = np.random.default_rng(0).integers(0, 256, (rows, cols, 3), dtype=np.uint8)
+    plan = bb.GaussPlan(rows, cols, 50.0, mode)
+    d_in = torch.from_numpy(img).cuda()
+    plan.run(d_in)
+    torch.cuda.synchronize()
+    out = d_in.cpu().numpy()
+    del d_in
+    plan.close()
+    ref, who = _cpu_reference_blur(oracle, img, 50.0, mode)
+    mx, nbad, nne = 0, 0, 0
+    for r0 in range(0, rows, 1024):                      # chunked: no 1.6 GB int temporaries
+        d = np.abs(out[r0:r0 + 1024].astype(np.int16) - ref[r0:r0 + 1024].astype(np.int16))
+        mx = max(mx, int(d.max())); nbad += int((d > 1).sum()); nne += int((d > 0).sum())
+    frac = nne / out.size
+    with capfd.disabled():
+        print(f"\n[C3 mode {mode} vs {who}] max |diff| = {mx} LSB, bytes differing = {nne} ({frac:.3e}), > 1 LSB: {nbad}")
+    assert mx <= 1 and nbad == 0
+    assert frac < 1e-3
+
+
+@pytest.mark.parametrize("rows,cols,sigma", [(2160, 3840, 25.0), (16384, 16384, 50.0)])
+def test_gauss_float32_intermediate_c2_c3(bb, oracle, torch, rows, cols, sigma, capfd):
+    """float32 row-pass intermediate (the reference's `resf`, Source.cpp:536) at BASELINE configs 2
+    and 3: max abs error against the oracle's full-length float32 FFT row pass, tolerance 1e-5 of the
+    0..255 data range (north_star "1e-5 relative" read as relative to full scale)."""
+    img = np.random.default_rng(0).integers(0, 256, (rows, cols, 3), dtype=np.uint8)
+    oracle.set_num_threads(os.cpu_count() or 1)
+    _, rp, _ = oracle.gauss_blur_1d(img, sigma, 0, want_f32=True)
+    plan = bb.GaussPlan(rows, cols, sigma, 0)
+    d_in = torch.from_numpy(img).cuda()
+    d_pl = torch.empty((3, rows, cols), dtype=torch.float32, device="cuda")
+    plan.rowpass_f32(d_in, d_pl)
+    torch.cuda.synchronize()
+    err, rel = 0.0, 0.0
+    for ch in range(3):
+        got = d_pl[ch].cpu().numpy()
+        e = np.abs(got - rp[ch])
+        err = max(err, float(e.max()))
+        rel = max(rel, float((e / np.maximum(np.abs(rp[ch]), 1.0)).max()))
+    with capfd.disabled():
+        print(f"\n[{rows}x{cols} sigma {sigma}] row-pass float32: max abs err {err:.3e} ({err / 255:.2e} of full scale), "
+              f"max err / max(|ref|, 1) {rel:.3e}; block length L = {plan.info['ols_L_row']}")
+    plan.close()
+    assert err <= F32_TOL
+
+
+def test_gauss_sharded_multi_gpu_bit_identity():
+    """With >= 2 visible GPUs: torchrun tools/diag/dist_check.py on 2 (and 8 if present) GPUs — the
+    sharded 16384 x 16384 sigma = 50 result (row stripes -> exchange -> column stripes) is bit-identical
+    to the single-GPU plan's on every rank."""
+    import subprocess
+    import sys
+    import torch as t
+    n = t.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    for world in sorted({2, 8 if n >= 8 else 2}):
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
+               "--master-port", str(29700 + world), os.path.join(root, "tools", "diag", "dist_check.py"), "--headline"]
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+        assert "16384x16384" in r.stdout and "identical=True" in r.stdout
+
+
 def test_gauss_float32_intermediate(bb, oracle, torch):
     for rows, cols, sigma, mode in [(240, 320, 5.0, 0), (135, 241, 6.0, 1), (1080, 1920, 5.0, 0)]:
         img = synth("noise", rows, cols, 4)

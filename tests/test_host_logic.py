@@ -188,6 +188,70 @@ def test_sharded_host_logic_gloo_world2(tmp_path):
         assert p.returncode == 0, o
 
 
+_GLOO_BATCH_WORKER = r'''
+import os, sys
+import numpy as np, torch, torch.distributed as dist
+sys.path.insert(0, os.environ["BLUR_ROOT"]); sys.path.insert(0, os.path.join(os.environ["BLUR_ROOT"], "tests"))
+from oracle_lib import Oracle
+from blur_algorithms_b200.dist import ShardedBatch
+dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%s" % os.environ["BLUR_PORT"],
+                        rank=int(os.environ["RANK"]), world_size=int(os.environ["WORLD_SIZE"]))
+rank, n = dist.get_rank(), dist.get_world_size()
+o = Oracle()
+batch = 7                                                    # odd: the shares are ragged
+imgs = np.stack([np.random.default_rng(100 + i).integers(0, 256, (40, 56, 3), dtype=np.uint8) for i in range(batch)])
+sb = ShardedBatch(batch)                                     # rank / world size from the process group
+assert sb.indices == list(range(rank, batch, n)) and len(sb) == len(sb.indices)
+mine = sb.take(imgs)
+assert mine.shape[0] == len(sb) and all(np.array_equal(mine[j], imgs[i]) for j, i in enumerate(sb.indices))
+# the per-rank work, with the CPU oracle standing in for fastboxblur_batch (no GPU here)
+done = [o.fastboxblur(im, 9, 2) for im in mine]
+full = sb.gather(done)
+assert len(full) == batch
+for i in range(batch):
+    assert np.array_equal(full[i], o.fastboxblur(imgs[i], 9, 2)), i
+assert ShardedBatch(0, 0, 2).indices == [] and ShardedBatch(1, 1, 2).indices == []
+dist.barrier()
+print("rank", rank, "ok")
+'''
+
+
+def test_sharded_batch_gloo_world2(tmp_path):
+    """ShardedBatch (image i -> rank i mod P, no collective on the data path): shares, ragged batch,
+    reassembly in image order, at world size 2 over gloo."""
+    import socket
+    s = socket.socket(); s.bind(("127.0.0.1", 0)); port = s.getsockname()[1]; s.close()
+    script = tmp_path / "worker.py"
+    script.write_text(_GLOO_BATCH_WORKER)
+    procs = []
+    for r in range(2):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE="2", BLUR_PORT=str(port), BLUR_ROOT=ROOT, OMP_NUM_THREADS="2")
+        procs.append(subprocess.Popen([sys.executable, str(script)], env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT))
+    outs = [p.communicate(timeout=300)[0].decode() for p in procs]
+    for p, o in zip(procs, outs):
+        assert p.returncode == 0, o
+
+
+def test_bench_reference_arm_full_size_and_threads():
+    """bench.py --impl reference: times the workload's full image (no sub-image), forces the OpenMP
+    thread count itself (torchrun exports OMP_NUM_THREADS=1) and labels config / sample accordingly."""
+    import json
+    env = dict(os.environ, OMP_NUM_THREADS="1", RANK="0", WORLD_SIZE="2")
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1",
+                        "--warmup", "0", "--workload", "gauss_c1"], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = json.loads(r.stdout.strip().splitlines()[-1])
+    cores = len(os.sched_getaffinity(0))
+    assert line["impl"] == "reference" and line["cpu_baseline"]["cores"] == cores and line["config"]["threads"] == cores
+    assert line["config"]["rows"] == 1080 and "1080x1920" in line["cpu_baseline"]["sample"] and "whole workload image" in line["cpu_baseline"]["sample"]
+    assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["steps"] == 1 and line["warmup"] == 0
+    # rank != 0 exits 0 without work
+    env["RANK"] = "1"
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference", "--gpus", "2", "--steps", "1",
+                        "--warmup", "0", "--workload", "gauss_c1"], env=env, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0 and r.stdout.strip() == ""
+
+
 def test_cli_ppm_roundtrip(tmp_path):
     """CLI image I/O (reference: cv::imread / cv::imwrite, Source.cpp:621,636): P6 round trip, BGR order."""
     from blur_algorithms_b200 import cli

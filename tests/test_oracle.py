@@ -199,6 +199,21 @@ def test_oracle_vs_reference_live(oracle, reference):
         assert np.array_equal(oracle.fastboxblur(im, 9, 2), reference.test(im, 4, 3.0))
 
 
+def test_oracle_equals_reference_at_1080p_and_4k(oracle):
+    """BASELINE configs 1 and 2: the C restatement reproduces the reference's own output (oracle/_ref,
+    generated by tests/golden/make_golden_large.py) bit for bit — SHA-256 of the whole image."""
+    import hashlib
+    from util import LARGE_GOLDEN_CASES, large_golden, lattice
+    gold = large_golden()
+    for rows, cols, sigma in LARGE_GOLDEN_CASES:
+        img = synth("noise", rows, cols, 0)
+        for mode, name in ((0, "pocketfft1d"), (1, "pffft")):
+            out = oracle.gauss_blur_1d(img, sigma, mode)
+            key = f"noise_{rows}x{cols}_s{sigma}_{name}"
+            assert hashlib.sha256(out.tobytes()).digest() == gold[key + "_sha256"].tobytes(), key
+            assert np.array_equal(lattice(out), gold[key + "_lattice"]), key
+
+
 def test_pffft_quirk_is_rank_one_correction(oracle):
     """The identity DESIGN.md 3.1a builds on: the oracle's pffft-mode row pass (Source.cpp:414-427)
     equals the exact row pass + c (-1)^x A per line, A = weighted alternating sum of the line

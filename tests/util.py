@@ -40,6 +40,23 @@ GOLDEN_CASES = [
 GOLDEN_BOX_CASES = [("noise", 64, 96, 3.0), ("noise", 100, 75, 2.0), ("stripes", 96, 128, 4.0), ("noise", 135, 241, 5.0)]
 
 
+# BASELINE.json configs 1 and 2: outputs of the reference itself (tests/golden/make_golden_large.py)
+LARGE_GOLDEN_CASES = [(1080, 1920, 5.0), (2160, 3840, 25.0)]
+
+
+def lattice(img: np.ndarray) -> np.ndarray:
+    """The sampled pixels stored per large golden case: a 37 x 53 lattice over the image plus the
+    first / last two rows and columns on a finer lattice (borders are where reflect-101 lives)."""
+    rows, cols = img.shape[:2]
+    parts = [img[::37, ::53].reshape(-1, 3), img[:2, ::7].reshape(-1, 3), img[rows - 2:, ::7].reshape(-1, 3),
+             img[::5, :2].reshape(-1, 3), img[::5, cols - 2:].reshape(-1, 3)]
+    return np.concatenate(parts)
+
+
+def large_golden():
+    return np.load(os.path.join(GOLDEN, "reference_large.npz"))
+
+
 def golden_outputs():
     return np.load(os.path.join(GOLDEN, "reference_outputs.npz"))
 

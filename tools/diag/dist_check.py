@@ -14,7 +14,10 @@ dev = torch.device("cuda", local)
 dist.init_process_group("nccl", device_id=dev)
 rank, world = dist.get_rank(), dist.get_world_size()
 ok = True
-for rows, cols, sigma in [(1080, 1920, 5.0), (2160, 3840, 25.0), (1001, 1531, 9.0), (4096, 4096, 50.0)]:
+cases = [(1080, 1920, 5.0), (2160, 3840, 25.0), (1001, 1531, 9.0), (4096, 4096, 50.0)]
+if "--headline" in sys.argv:        # BASELINE config 3 (tests/test_gpu_parity.py::test_gauss_sharded_multi_gpu_bit_identity)
+    cases = [(1001, 1531, 9.0), (16384, 16384, 50.0)]
+for rows, cols, sigma in cases:
     img = np.random.default_rng(7).integers(0, 256, (rows, cols, 3), dtype=np.uint8)
     sb = ShardedGaussBlur(rows, cols, sigma, bb.NYQUIST_EXACT, device=dev)
     g = sb.geom
