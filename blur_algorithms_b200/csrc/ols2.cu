@@ -22,16 +22,24 @@ cudaError_t launch_ols2_row(const OlsRowIO& io, const float2* tw2, const float* 
     constexpr int R2 = 32;
     constexpr int smem = ols2_row_smem_bytes<R2>();
     const bool sharded = io.nparts > 1;
-    cudaError_t e = sharded ? opt_in_smem(ols2_row_kernel<R2, true>, smem) : opt_in_smem(ols2_row_kernel<R2, false>, smem);
+    // bulk epilogue: every piece a bulk copy moves must be 16-byte aligned at both ends
+    static const int bulk_env = std::getenv("BLUR_B200_ROW_BULK") ? std::atoi(std::getenv("BLUR_B200_ROW_BULK")) : -1;
+    const int cpart = sharded ? io.cpart : io.qpitch;
+    bool bulk = io.ax.V % 4 == 0 && io.cols % 4 == 0 && io.qpitch % 4 == 0 && cpart % 4 == 0 && io.ax.V <= cpart &&
+                reinterpret_cast<uintptr_t>(io.q) % 16 == 0;
+    for (int k = 0; bulk && sharded && io.peer && k < io.nparts; ++k) bulk = reinterpret_cast<uintptr_t>(io.qpeer[k]) % 16 == 0;
+    if (bulk_env == 0) bulk = false;
+    const void* fn = sharded ? (bulk ? (const void*)ols2_row_kernel<R2, true, true> : (const void*)ols2_row_kernel<R2, true, false>)
+                             : (bulk ? (const void*)ols2_row_kernel<R2, false, true> : (const void*)ols2_row_kernel<R2, false, false>);
+    cudaError_t e = cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) return e;
     static const int ctas_env = std::getenv("BLUR_B200_ROW_CTAS") ? std::atoi(std::getenv("BLUR_B200_ROW_CTAS")) : 0;
     const int per_sm = ctas_env > 0 ? std::min(ctas_env, BLUR_OLS2_ROW_CTAS) : BLUR_OLS2_ROW_CTAS;
     const int grid = std::min((io.nunits + kOls2RowWarps - 1) / kOls2RowWarps, num_sms * per_sm);
     if (grid <= 0) return cudaSuccess;
-    if (sharded)
-        ols2_row_kernel<R2, true><<<grid, 32 * kOls2RowWarps, smem, stream>>>(io, tw2, kt);
-    else
-        ols2_row_kernel<R2, false><<<grid, 32 * kOls2RowWarps, smem, stream>>>(io, tw2, kt);
+    void* args[] = {const_cast<OlsRowIO*>(&io), &tw2, &kt};
+    e = cudaLaunchKernel(fn, dim3(grid), dim3(32 * kOls2RowWarps), args, smem, stream);
+    if (e != cudaSuccess) return e;
     return cudaGetLastError();
 }
 

@@ -81,9 +81,8 @@ BLUR_HD void ols2_pass2(cplx* __restrict__ sx, int k1, const cplx* __restrict__ 
 // pass 1: item n2 reads the staged interleaved bytes of the unit's two lines (OlsRowIO::Ctx),
 // channel ch, and leaves A[k1][n2] in the tile.
 template <int R2>
-BLUR_HD void ols2_row_pass1(cplx* __restrict__ tile, const OlsRowIO::Ctx& c, int ch, int n2)
+BLUR_HD void ols2_row_pass1_compute(const OlsRowIO::Ctx& c, int ch, int n2, cplx (&x)[kOls2R1])
 {
-    cplx x[kOls2R1];
     const uint8_t* pa = c.raw + c.ia + 3 * n2 + ch;
     const int db = c.ib - c.ia;
 #ifdef __CUDA_ARCH__
@@ -112,9 +111,22 @@ BLUR_HD void ols2_row_pass1(cplx* __restrict__ tile, const OlsRowIO::Ctx& c, int
     }
     CDftV<kOls2R1>::fwd(x);
 #endif
+}
+
+template <int R2>
+BLUR_HD void ols2_row_pass1_store(cplx* __restrict__ tile, int n2, const cplx (&x)[kOls2R1])
+{
     cplx* col = tile + n2;
 #pragma unroll
     for (int k = 0; k < kOls2R1; ++k) col[(R2 + 1) * k] = x[k];
+}
+
+template <int R2>
+BLUR_HD void ols2_row_pass1(cplx* __restrict__ tile, const OlsRowIO::Ctx& c, int ch, int n2)
+{
+    cplx x[kOls2R1];
+    ols2_row_pass1_compute<R2>(c, ch, n2, x);
+    ols2_row_pass1_store<R2>(tile, n2, x);
 }
 
 // pass 3: item n2 -> Q.  Output j of the item is image column s + R2 j + n2 of lines (ra, ra+1).

@@ -75,8 +75,79 @@ __device__ __forceinline__ void ols2_row_stage(const OlsRowIO& io, int pair, int
     }
 }
 
-// SHARDED: the epilogue addresses the parts / peer buffers of a multi-GPU plan (io.nparts > 1)
+// ---- bulk epilogue --------------------------------------------------------------------------
+// Pass 3 with its outputs leaving through the TMA engine: once every lane holds its tile column in
+// registers the tile memory is dead, so the kept outputs are written there in natural order (line a
+// as floats [0, nvalid), line b behind it) and up to four lanes each issue ONE bulk shared->global
+// copy (cp.async.bulk, SASS UBLKCP) per line and destination part — 2.7 KB per copy at sigma = 50
+// instead of sixty-four 4-byte stores per lane.  In a sharded plan the destination is the owning
+// GPU's Q over NVLink: the exchange (the distributed flip_block, Source.cpp:540) rides out of the
+// FFT kernel tile by tile, in large packets, without a send buffer and without stalling the SM on
+// remote store credits.  Needs 16-byte aligned pieces: V, cols, cpart and qpitch multiples of 4.
+__device__ __forceinline__ void bulk_store(const void* gdst, const void* ssrc, uint32_t bytes)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gdst), "r"(smem_u32(ssrc)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
+__device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
+
+constexpr int kOls2BulkB = 1056;       // float offset of line b's outputs in the tile (tile = 2112 floats)
+
 template <int R2, bool SHARDED>
+__device__ __forceinline__ void ols2_row_pass3_bulk(cplx* __restrict__ tile, const OlsRowIO& io, const OlsRowIO::Ctx& c, int ch,
+                                                    int lane, const cplx* __restrict__ w)
+{
+    cplx x[kOls2R1];
+    const cplx* col = tile + lane;
+#pragma unroll
+    for (int k = 0; k < kOls2R1; ++k) x[k] = col[(R2 + 1) * k];
+    __syncwarp();                                       // every lane's column is in registers: the tile is free
+    CDftV<kOls2R1>::bwd_twc(x, w);
+    if (io.corr) {
+        const float* cr = io.corr + static_cast<size_t>(ch) * io.corr_pitch + c.ra;
+        const float sg = ((c.s + lane) & 1) ? -1.f : 1.f;
+        const cplx cc = cpack(sg * cr[0], c.has_b ? sg * cr[1] : 0.f);
+#pragma unroll
+        for (int j = 0; j < kOls2R1; ++j) x[j] = cadd(x[j], cc);
+    }
+    const uint32_t keep = ols2_item_mask<R2>(lane, io.ax.halo, c.nvalid);
+    float* oa = reinterpret_cast<float*>(tile) + (lane - io.ax.halo);        // output i = R2 j + lane lands at float i - halo
+#pragma unroll
+    for (int j = 0; j < kOls2R1; ++j)
+        if (keep >> j & 1u) { oa[R2 * j] = cre(x[j]); oa[kOls2BulkB + R2 * j] = cim(x[j]); }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    __syncwarp();
+    // lane = 2 * line + segment
+    const int line = lane >> 1, seg = lane & 1;
+    if (lane < 4 && (line == 0 || c.has_b)) {
+        const int x_start = c.s + io.ax.halo;           // first kept column of the block
+        const int nparts = SHARDED ? io.nparts : 1;
+        int o0 = 0, n = c.nvalid, part = 0;
+        if (SHARDED) {
+            part = c.part0;
+            const int n0 = min(c.nvalid, c.b1 - x_start);       // columns that stay in part0
+            if (seg == 0) n = n0; else { o0 = n0; n = c.nvalid - n0; ++part; }
+        } else if (seg) {
+            n = 0;
+        }
+        if (n > 0) {
+            const int xx = x_start + o0;
+            float* d;
+            if (SHARDED && io.peer)
+                d = io.qpeer[part] + (static_cast<size_t>(ch * nparts + io.rank) * io.srows + c.ra + line) * io.qpitch + (xx - part * io.cpart);
+            else
+                d = c.qa + (static_cast<size_t>(ch) * nparts + part) * io.srows * io.qpitch + static_cast<size_t>(line) * io.qpitch +
+                    (xx - part * io.cpart);
+            bulk_store(d, reinterpret_cast<const float*>(tile) + line * kOls2BulkB + o0, static_cast<uint32_t>(n) * 4u);
+        }
+    }
+    bulk_commit();
+}
+
+// SHARDED: the epilogue addresses the parts / peer buffers of a multi-GPU plan (io.nparts > 1)
+// BULK: epilogue through bulk shared->global copies (ols2_row_pass3_bulk)
+template <int R2, bool SHARDED, bool BULK>
 __global__ void __launch_bounds__(32 * kOls2RowWarps, BLUR_OLS2_ROW_CTAS)
 ols2_row_kernel(const __grid_constant__ OlsRowIO io, const float2* __restrict__ tw2_, const float* __restrict__ kt)
 {
@@ -110,7 +181,15 @@ ols2_row_kernel(const __grid_constant__ OlsRowIO io, const float2* __restrict__ 
         }
 #pragma unroll 1
         for (int ch = 0; ch < 3; ++ch) {
-            ols2_row_pass1<R2>(tile, ctx, ch, lane);
+            {
+                cplx x[kOls2R1];
+                ols2_row_pass1_compute<R2>(ctx, ch, lane, x);
+                if (BULK) {                             // the previous transform's bulk copies have read the tile
+                    bulk_wait_read();
+                    __syncwarp();
+                }
+                ols2_row_pass1_store<R2>(tile, lane, x);
+            }
             __syncwarp();
             if (ch == 2) {
                 // the staged bytes are consumed: fetch the next unit's underneath passes 2 and 3
@@ -119,11 +198,15 @@ ols2_row_kernel(const __grid_constant__ OlsRowIO io, const float2* __restrict__ 
             }
             ols2_pass2<R2, 1>(tile, lane, w, kts);
             __syncwarp();
-            ols2_row_pass3<R2, SHARDED>(tile, io, ctx, ch, lane, w);
-            // no barrier: the next pass 1 of this lane writes exactly the slots it has just read
+            if (BULK)
+                ols2_row_pass3_bulk<R2, SHARDED>(tile, io, ctx, ch, lane, w);
+            else
+                ols2_row_pass3<R2, SHARDED>(tile, io, ctx, ch, lane, w);
+            // non-bulk: no barrier, the next pass 1 of this lane writes exactly the slots it has just read
         }
         pair = npair; b = nb;
     }
+    if (BULK) bulk_wait_all();                          // the last copies have left shared memory and are performed
 }
 
 // ---- column pass ------------------------------------------------------------------------------

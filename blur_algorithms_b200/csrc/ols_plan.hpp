@@ -42,13 +42,16 @@ inline bool choose_ols_axis(int len, int pad, int align, int max_r0, OlsAxis& ax
 // Two-factor kernels (ols2_kernels.cuh): L = 32 * R2 with R2 = 32, halo = pad exactly.  Chosen when at
 // least `min_frac` of a block is valid output (narrow and medium kernels: sigma <= ~65); wider
 // kernels keep the three-factor kernels and their longer blocks.
-inline bool choose_ols2_axis(int len, int pad, OlsAxis& ax, double min_frac = 0.55)
+// `even_halo`: round the halo up to an even number so that V is a multiple of 4 and every block's
+// first output is 16-byte aligned in Q (row axis: the epilogue leaves through bulk shared->global copies).
+inline bool choose_ols2_axis(int len, int pad, OlsAxis& ax, bool even_halo = false, double min_frac = 0.55)
 {
     const int R2 = 32, L = 32 * R2;
-    const int V = L - 2 * pad;
+    const int halo = even_halo ? pad + (pad & 1) : pad;
+    const int V = L - 2 * halo;
     if (V < static_cast<int>(min_frac * L)) return false;
     ax = OlsAxis{};
-    ax.R0 = L / 256; ax.L = L; ax.halo = pad; ax.V = V; ax.nblocks = (len + V - 1) / V; ax.len = len; ax.pad = pad; ax.R2 = R2;
+    ax.R0 = L / 256; ax.L = L; ax.halo = halo; ax.V = V; ax.nblocks = (len + V - 1) / V; ax.len = len; ax.pad = pad; ax.R2 = R2;
     return true;
 }
 
@@ -87,7 +90,7 @@ inline ShardGeom shard_geometry(const GaussGeometry& gg, int nyquist_mode, int r
         const bool want_row = !e || !std::strcmp(e, "1") || !std::strcmp(e, "row");
         const bool want_col = !e || !std::strcmp(e, "1") || !std::strcmp(e, "col");
         OlsAxis a2;
-        if (want_row && choose_ols2_axis(cols, gg.pad, a2)) g.ols_row = a2;
+        if (want_row && choose_ols2_axis(cols, gg.pad, a2, true)) g.ols_row = a2;
         if (want_col && choose_ols2_axis(rows, gg.pad, a2)) g.ols_col = a2;
     }
     const int cp_total = (cols + 1) / 2;

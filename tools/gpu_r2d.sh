@@ -17,7 +17,7 @@ run evictlast BLUR_B200_LIB=$PWD/blur_algorithms_b200/libblur_b200_h2.so
 EXTRA="--sigma 5"
 run sigma5 X=1
 EXTRA=""
-for v in "X=1" "BLUR_B200_L2_FETCH=32" "BLUR_B200_L2_FETCH=128" "BLUR_B200_LIB=$PWD/blur_algorithms_b200/libblur_b200_h1.so" "BLUR_B200_LIB=$PWD/blur_algorithms_b200/libblur_b200_h2.so"; do
+for v in "X=1" "BLUR_B200_ROW_BULK=0" "BLUR_B200_L2_FETCH=32" "BLUR_B200_L2_FETCH=128" "BLUR_B200_LIB=$PWD/blur_algorithms_b200/libblur_b200_h1.so" "BLUR_B200_LIB=$PWD/blur_algorithms_b200/libblur_b200_h2.so"; do
   echo "-- $v"; env $v timeout 300 python tools/diag/pass_time.py --variants "OLS2=1" 2>&1 | tail -1
 done
 timeout 600 python -m pytest tests -m gpu -x -q -k "not c3_full and not c2_c3" > $O/${T}_pytest.log 2>&1; tail -3 $O/${T}_pytest.log
