@@ -147,7 +147,7 @@ def cpu_reference_run(wl: dict, steps: int, warmup: int):
     else:
         nimg = min(wl["batch"], 16)                                      # bounded sample of the batch
         imgs = [rng.integers(0, 256, (rows, cols, 3), dtype=np.uint8) for _ in range(nimg)]
-        ns = float(np.sqrt(wl["ksize"]))                                 # Test(flag=4): ksize = nsmooth * nsmooth
+        ns = float(np.sqrt(wl["ksize"] + 0.5))                           # Test(flag=4): ksize = int(nsmooth * nsmooth)
         assert int(ns * ns) == wl["ksize"]
         if use_ref:
             fn = lambda: [impl.test(im, 4, ns) for im in imgs]           # noqa: E731

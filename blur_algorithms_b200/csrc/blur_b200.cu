@@ -820,7 +820,7 @@ int run_col_pass_to_u(blur_b200_plan* p, const float* d_q_chunks, cudaStream_t s
         if (blk_end < 0) blk_end = io.ax.nblocks;
         io.b0 = blk_begin;
         io.nbl = blk_end - blk_begin;
-        io.nunits = io.ax.R2 ? io.nbl * 3 * cdiv(io.noct, 2) : io.nbl * 3 * io.noct;
+        io.nunits = io.ax.R2 ? ols2_col_npairs(io.noct, io.nbl) : io.nbl * 3 * io.noct;
         if (p->quirk_ols) {
             io.corr = p->d_corr_col; io.corr_pitch = p->qpitch;
         }

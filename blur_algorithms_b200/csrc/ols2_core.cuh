@@ -264,9 +264,20 @@ BLUR_HD void ols2_col_pass3_store(const OlsColIO& io, const OlsColIO::Ctx& c, in
     }
 }
 
+// Pair q of the column pass -> (strip, block).  A strip is (octet pair j, channel): 16 float columns =
+// 64 bytes of a Q row.  DRAM hands L2 whole 128-byte lines, and at this kernel's fill rate a line lives
+// in L2 for only a few tens of microseconds, so the two pairs that share a line (j = 2g, 2g+1) are walked
+// back to back, then the next block of the same strips (its halo rows are still resident), then the
+// channels, then the next line group.  io.nunits = 2 * nbl * 3 * ceil(ceil(noct / 2) / 2).
 struct Ols2ColWalk {
-    int strip, b;        // current pair
-    BLUR_HD void next(int nbl) { if (++b == nbl) { b = 0; ++strip; } }
+    int strip, b;
+    BLUR_HD static Ols2ColWalk at(int q, int nbl)
+    {
+        const int h = q & 1, r = q >> 1;
+        const int b = r % nbl, rest = r / nbl;
+        const int ch = rest % 3, g = rest / 3;
+        return Ols2ColWalk{3 * (2 * g + h) + ch, b};
+    }
 };
 
 // sub-unit context of (strip, b, member m): channel = strip % 3, octet = 2 * (strip / 3) + m

@@ -265,7 +265,7 @@ __device__ __forceinline__ void ols2_col_fetch(const OlsColIO& io, const OlsColI
 
 __device__ __forceinline__ void cp_async_wait_1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 
-// io.nunits = number of (strip, block) pairs = nstrips * io.nbl, nstrips = 3 * ceil(noct / 2)
+// io.nunits = ols2_col_npairs(noct, nbl) (strip, block) pairs, walked in the order Ols2ColWalk::at gives
 template <int R2>
 __global__ void __launch_bounds__(128, BLUR_OLS2_COL_CTAS)
 ols2_col_kernel(const __grid_constant__ OlsColIO io, const float2* __restrict__ tw2_, const float* __restrict__ kt)
@@ -284,7 +284,7 @@ ols2_col_kernel(const __grid_constant__ OlsColIO io, const float2* __restrict__ 
     // this CTA's run of pairs
     const long long np = io.nunits;
     const int q0 = static_cast<int>(np * blockIdx.x / gridDim.x), q1 = static_cast<int>(np * (blockIdx.x + 1) / gridDim.x);
-    Ols2ColWalk cur{q0 / io.nbl, q0 % io.nbl}, nxt = cur;
+    Ols2ColWalk cur = Ols2ColWalk::at(q0, io.nbl), nxt = Ols2ColWalk::at(q0 + 1, io.nbl);
     // prologue: both members of the first pair
 #pragma unroll
     for (int m = 0; m < 2; ++m) {
@@ -294,7 +294,6 @@ ols2_col_kernel(const __grid_constant__ OlsColIO io, const float2* __restrict__ 
         }
         cp_async_commit();
     }
-    nxt.next(io.nbl);
     __syncthreads();
     for (int q = q0; q < q1; ++q) {
 #pragma unroll 1
@@ -326,7 +325,7 @@ ols2_col_kernel(const __grid_constant__ OlsColIO io, const float2* __restrict__ 
             if (ctx.valid) ols2_col_pass3_store<R2>(io, ctx, X, t, x, w);
         }
         cur = nxt;
-        nxt.next(io.nbl);
+        nxt = Ols2ColWalk::at(q + 2, io.nbl);
     }
 }
 

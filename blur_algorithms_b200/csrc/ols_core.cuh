@@ -499,4 +499,7 @@ BLUR_HD void ols_col_patch(cplx* __restrict__ s, int e, int s0, const OlsAxis& a
     s[4 * ols_pad(i) + X] = src < 0 ? czero() : s[4 * ols_pad(src - s0) + X];
 }
 
+// (strip, block) pairs of the two-factor column pass, see Ols2ColWalk (ols2_core.cuh)
+BLUR_HD int ols2_col_npairs(int noct, int nbl) { return 2 * nbl * 3 * ((((noct + 1) / 2) + 1) / 2); }
+
 }  // namespace blurb200

@@ -186,7 +186,8 @@ static void ols2_col_units(const OlsColIO& io, const Ols2Tables& T)
         for (int unit = 0; unit < 2 * io.nunits; ++unit) {
             // sub-unit = member m of the (strip, block) pair q, as ols2_col_kernel walks them
             const int q = unit >> 1, m = unit & 1;
-            const OlsColIO::Ctx ctx = ols2_col_ctx(io, q / io.nbl, q % io.nbl, m);
+            const Ols2ColWalk wk = Ols2ColWalk::at(q, io.nbl);
+            const OlsColIO::Ctx ctx = ols2_col_ctx(io, wk.strip, wk.b, m);
             if (!ctx.valid) continue;
             std::fill(smem.begin(), smem.end(), make_float2(-777.f, 777.f));
             for (int i = 0; i < L; ++i)
@@ -240,7 +241,7 @@ static int ols_col_pass(const float* q_recv, uint8_t* out_cols, const GaussGeome
     io.u = U.data(); io.rows = rows; io.ax = sg.ols_col; io.nunits = io.ax.nblocks * 3 * io.noct;
     io.q = q_recv; io.qpitch = sg.qpitch; io.rows_total = nranks * sg.stripe_rows;
     if (io.ax.R2 == 32) {
-        io.nbl = io.ax.nblocks; io.nunits = io.nbl * 3 * ((io.noct + 1) / 2);
+        io.nbl = io.ax.nblocks; io.nunits = ols2_col_npairs(io.noct, io.nbl);
         ols2_col_units<32>(io, Ols2Tables(32, sigma, gg.ksize));
     } else {
         const OlsTables T(io.ax.R0, sigma, gg.ksize);
