@@ -378,6 +378,25 @@ def test_box_bit_exact_small(bb, oracle):
         bb.fastboxblur(np.zeros((10, 10, 3), np.uint8), 10, 10, 3, 25, 1)
 
 
+def test_box_packed_kernel_geometries(bb):
+    """box2_tile_kernel (C = 3, 4; 16-byte rows): every stream alignment (radius 1..21, 31, 63), several
+    tiles in x and y, narrow last tile, border tiles, against the numpy restatement (bit-exact)."""
+    cases = [(3, r, (70, 176)) for r in range(1, 22)] + [(4, r, (50, 132)) for r in range(1, 18)]
+    cases += [(3, 15, (300, 1200)), (3, 31, (200, 688)), (3, 63, (150, 352)), (4, 7, (260, 520)), (4, 40, (140, 260)),
+              (3, 5, (129, 176)), (3, 2, (33, 16 * 11))]
+    for ch, r, shape in cases:
+        rng = np.random.default_rng(100 * ch + r)
+        img = rng.integers(0, 256, shape + (ch,), dtype=np.uint8)
+        if r % 5 == 0:
+            img[:] = 255                                    # saturated sums
+        for passes in ((1, 2) if r in (3, 15) else (1,)):
+            out = img.copy()
+            bb.fastboxblur(out, shape[1], shape[0], ch, 2 * r + 1, passes)
+            want = box_numpy(img, 2 * r + 1, passes)
+            assert np.array_equal(out, want), (ch, r, shape, passes, int(np.abs(out.astype(int) - want).max()),
+                                               np.argwhere(out != want)[:4].tolist())
+
+
 def test_box_bit_exact_1080p_batch(bb, oracle, torch):
     """BASELINE config 5 shape (radius 15, 2 passes), a batch of 8 images, against the oracle."""
     imgs = np.stack([synth("noise", 1080, 1920, s) for s in range(8)])
