@@ -273,8 +273,10 @@ def dft_image(image: np.ndarray, nsmooth: float = 0.1, want_f32: bool = False):
 
 def Test(image: np.ndarray, flag: int = 0, nsmooth: float = 5) -> None:
     """Test(cv::Mat& image, int flag, double nsmooth), Source.cpp:574-608: 5 pocketfft_1D,
-    4 fastboxblur (ksize = nsmooth*nsmooth, 2 passes), 3 pffft_, 2 pocketfft_2D.  Flag 1 (the
-    OpenCV comparison line) is outside the hot path and raises."""
+    4 fastboxblur (ksize = nsmooth*nsmooth, 2 passes), 3 pffft_, 2 pocketfft_2D.  Any other flag is the
+    reference's OpenCV comparison line (`cv::GaussianBlur(image, image, Size(0, 0), nsmooth)`, :596-603):
+    host OpenCV through `cv2` when it is importable, an error otherwise -- it is a comparison baseline,
+    not part of the accelerated path."""
     if flag == 5:
         pocketfft_1D(image, nsmooth)
     elif flag == 4:
@@ -285,7 +287,11 @@ def Test(image: np.ndarray, flag: int = 0, nsmooth: float = 5) -> None:
     elif flag == 2:
         pocketfft_2D(image, nsmooth)
     else:
-        raise BlurB200Error(_lib.EINVAL, "flag 1 (cv::GaussianBlur / cv::blur) is not part of the hot path")
+        try:
+            import cv2
+        except ImportError:
+            raise BlurB200Error(_lib.EINVAL, "flag 1 is the reference's OpenCV baseline (cv::GaussianBlur); cv2 is not importable here") from None
+        cv2.GaussianBlur(image, (0, 0), nsmooth, dst=image)
 
 
 def kernel_launches() -> int:

@@ -142,8 +142,14 @@ def sweep(image: np.ndarray, flag: int) -> None:
             plan.close()
         else:
             t0 = time.perf_counter()
-            run_test(img, flag, sigma if flag == 1 else round(math.sqrt(sigma)) | 1, quiet=True)
+            # Source.cpp:627-634 calls Test(image, flag, sqrt(x)) for every flag: FastBoxBlur gets ksize = int(nsmooth^2) ~ x
+            run_test(img, flag, sigma, quiet=True)
             line["host_call_ms"] = (time.perf_counter() - t0) * 1e3
+            if flag == 4:
+                k = 2 * ((int(sigma * sigma) - 1) // 2) + 1
+                line["ksize"] = k
+                # k <= 127: packed tile kernel; wider windows: tile kernel while the staged rows fit shared memory, else the two-kernel path
+                line["box_path"] = "packed tile kernel" if k <= 127 else "wide-window paths (boxblur.cu dispatcher)"
         line["megapixels_per_s"] = x * y / 1e3 / line.get("device_ms", line["host_call_ms"])
         print(json.dumps(line), flush=True)
         x += 225

@@ -196,8 +196,16 @@ struct Box2Args {
     size_t img_stride;
 };
 
-__device__ __forceinline__ uint32_t box2_even(uint32_t v) { return v & 0x00FF00FFu; }
+// The ALU pipe (PRMT / LOP3 / IADD3 / SHF, 16 lanes per scheduler) is this kernel's bound, so everything
+// that can be phrased as a multiply-add is: even(v) = v - 256 * odd(v), the byte packing of the rounded
+// results, and every plain add go to the FMA pipe as IMAD.
 __device__ __forceinline__ uint32_t box2_odd(uint32_t v) { return __byte_perm(v, 0u, 0x4341); }
+__device__ __forceinline__ uint32_t box2_mad(uint32_t a, uint32_t b, uint32_t c)
+{
+    uint32_t d;
+    asm("mad.lo.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
 
 __device__ __forceinline__ uint32_t box2_round4(uint32_t e, uint32_t o, float inv, float cb)
 {
@@ -214,33 +222,37 @@ __device__ __forceinline__ uint32_t box2_round4(uint32_t e, uint32_t o, float in
         "mov.b64 {%0, %1}, a;\nmov.b64 {%2, %3}, b;\n}"
         : "=r"(u0), "=r"(u1), "=r"(u2), "=r"(u3)
         : "r"(f0), "r"(f1), "f"(inv), "f"(cb), "r"(f2), "r"(f3), "f"(8388608.f));
-    return __byte_perm(__byte_perm(u0, u1, 0x0040), __byte_perm(u2, u3, 0x0040), 0x5410);
+    // u_j = 0x4B000000 + q_j: q0 + 256 q1 + 65536 q2 + 2^24 q3 = u0 + 256 u1 + 65536 (u2 + 256 u3) - 0x4B000000 (mod 2^32)
+    return box2_mad(box2_mad(u3, 256u, u2), 65536u, box2_mad(u1, 256u, u0 - 0x4B000000u));
 }
 
-// one output word: slide the four sums by one word of new (nw) and old (ow) samples
+// one output word: slide the four sums by one word of new (nw) and old (ow) samples.
+// D = nw - ow as plain 32-bit words is sum_j (n_j - o_j) 256^j, so the even-byte differences are D - 256 * (odd differences).
 template <int C>
 __device__ __forceinline__ void box2_slide(uint32_t& e, uint32_t& o, uint32_t nw, uint32_t ow)
 {
-    const uint32_t de = box2_even(nw) - box2_even(ow), dod = box2_odd(nw) - box2_odd(ow);
+    const uint32_t dod = box2_odd(nw) - box2_odd(ow);
+    const uint32_t D = nw - ow;
     if (C == 3) {
-        const uint32_t e2 = o + de;
+        const uint32_t e2 = box2_mad(dod, 0xFFFFFF00u, o + D);
         o = __byte_perm(e, e2, 0x5432) + dod;
         e = e2;
     } else {
-        e += de;
+        e = box2_mad(dod, 0xFFFFFF00u, e + D);
         o += dod;
     }
 }
 template <int C>
 __device__ __forceinline__ void box2_prime(uint32_t& e, uint32_t& o, uint32_t nw)
 {
+    const uint32_t od = box2_odd(nw);
     if (C == 3) {
-        const uint32_t e2 = o + box2_even(nw);
-        o = __byte_perm(e, e2, 0x5432) + box2_odd(nw);
+        const uint32_t e2 = box2_mad(od, 0xFFFFFF00u, o + nw);
+        o = __byte_perm(e, e2, 0x5432) + od;
         e = e2;
     } else {
-        e += box2_even(nw);
-        o += box2_odd(nw);
+        e = box2_mad(od, 0xFFFFFF00u, e + nw);
+        o += od;
     }
 }
 
@@ -325,7 +337,10 @@ box2_tile_kernel(const __grid_constant__ Box2Args a)
         asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
                      ::"r"(d), "l"(src), "r"(nbytes), "r"(bar) : "memory");
     }
-    box2_mbar_wait(bar, 0);
+    // one thread polls (a spinning CTA would take issue slots from the two computing next to it); the
+    // barrier orders its acquire of the completed phase before everybody's reads
+    if (tid == 0) box2_mbar_wait(bar, 0);
+    __syncthreads();
     // mirrored bytes left / right of the image row (reflect-101 per pixel), taken from the staged row
     const int ul = -(rC + 16);
     if (x0b + ul < 0) {
@@ -346,7 +361,7 @@ box2_tile_kernel(const __grid_constant__ Box2Args a)
             srow[gb] = srow[max(2 * (a.w - 1) - j, 0) * C + c];
         }
     }
-    __syncthreads();
+    if (x0b + ul < 0 || x0b + a.TXB + rC > wb) __syncthreads();
 
     // ---- horizontal pass, in place
     if (tid < a.rows_t) {
@@ -367,20 +382,17 @@ box2_tile_kernel(const __grid_constant__ Box2Args a)
         uint32_t e = 0, o = 0;
         const int k = 2 * a.r + 1;
 #pragma unroll 4
-        for (int ry = 0; ry < k; ++ry) {
-            const uint32_t v = col[ry * pw];
-            e += box2_even(v);
-            o += box2_odd(v);
-        }
+        for (int ry = 0; ry < k; ++ry) box2_prime<4>(e, o, col[ry * pw]);
         const int ny = min(a.TY, a.h - y0);
-        uint8_t* op = dst + static_cast<size_t>(y0) * wb + x0b + 4 * tid;
-        const uint32_t* cn = col + k * pw;                     // sample entering the window of row j + 1
+        uint8_t* po = dst + static_cast<size_t>(y0) * wb + x0b + 4 * tid;
+        const uint32_t* pn = col + k * pw;                     // sample entering the window of row j + 1
+        const uint32_t* pc = col;                              // sample leaving it
 #pragma unroll 4
         for (int j = 0; j < ny; ++j) {
-            const uint32_t vn = cn[j * pw], vo = col[j * pw];      // staged rows 0 .. TY + 2r: always inside the tile's shared memory
-            *reinterpret_cast<uint32_t*>(op + static_cast<size_t>(j) * wb) = box2_round4(e, o, a.inv, a.cb);
-            e += box2_even(vn) - box2_even(vo);
-            o += box2_odd(vn) - box2_odd(vo);
+            const uint32_t vn = *pn, vo = *pc;                 // staged rows 0 .. TY + 2r: always inside the tile's shared memory
+            *reinterpret_cast<uint32_t*>(po) = box2_round4(e, o, a.inv, a.cb);
+            box2_slide<4>(e, o, vn, vo);
+            pn += pw; pc += pw; po += wb;
         }
     }
 }

@@ -6,6 +6,7 @@ Tolerances (BASELINE.json north_star): uint8 output within +-1 LSB of the refere
 float32 intermediates within 1e-5 relative (relative to the 0..255 data range: <= 255e-5);
 FastBoxBlur bit-exact.
 """
+import json
 import os
 
 import numpy as np
@@ -411,6 +412,45 @@ def test_box_bit_exact_1080p_batch(bb, oracle, torch):
     c = torch.full((2, 1080, 1920, 3), 131, dtype=torch.uint8, device="cuda")
     bb.fastboxblur_device(c, 1920, 1080, 3, 31, 2, 2, torch.empty_like(c))
     assert int(c.min()) == 131 and int(c.max()) == 131
+
+
+def test_box_vs_cv2_blur(bb):
+    """FastBoxBlur against cv2.blur(BORDER_REFLECT_101).  cv2.blur rounds once per 2-D pass,
+    FastBoxBlur after each 1-D pass, so the outputs may differ by one LSB per pass (parity with upstream
+    FastBoxBlur itself stays unpinned: its source is absent)."""
+    cv2 = pytest.importorskip("cv2")
+    for kind, shape in (("noise", (1080, 1920)), ("ramp", (300, 400))):
+        img = synth(kind, *shape)
+        for k, passes in ((31, 2), (5, 1), (9, 2), (15, 3)):
+            out = img.copy()
+            bb.fastboxblur(out, shape[1], shape[0], 3, k, passes)
+            ref = img.copy()
+            for _ in range(passes):
+                ref = cv2.blur(ref, (k, k), borderType=cv2.BORDER_REFLECT_101)
+            d = np.abs(out.astype(np.int16) - ref.astype(np.int16))
+            print(f"box k={k} passes={passes} {kind}: max |diff| vs cv2.blur {int(d.max())}, mean {float(d.mean()):.4f}")
+            assert int(d.max()) <= passes, (kind, k, passes, int(d.max()))
+
+
+def test_flag1_and_compare_cv2(bb, tmp_path, capsys):
+    """Test(flag = 1) is the reference's OpenCV line (Source.cpp:596-603); --compare-cv2 reports the
+    difference of the FFT blurs against it.  Documented bounds: smooth input within 2 LSB
+    everywhere; uniform noise (the worst case: the two kernels are truncated at different widths and OpenCV
+    filters uint8 images in fixed point) within 1 LSB on average at sigma >= 5."""
+    cv2 = pytest.importorskip("cv2")
+    from blur_algorithms_b200 import cli
+    img = synth("ramp", 480, 640)
+    a = img.copy()
+    bb.Test(a, 1, 5.0)
+    assert np.array_equal(a, cv2.GaussianBlur(img, (0, 0), 5.0))
+    for kind, flag, sigma, max_b, mean_b in (("ramp", 3, 5.0, 2, 0.5), ("ramp", 5, 5.0, 2, 0.5), ("noise", 5, 5.0, 8, 1.0),
+                                             ("noise", 2, 25.0, 4, 0.6)):
+        src = tmp_path / f"{kind}.png"
+        cv2.imwrite(str(src), synth(kind, 480, 640))
+        assert cli.main([str(flag), str(sigma), str(src), "-o", str(tmp_path / "out.png"), "--compare-cv2"]) == 0
+        line = [ln for ln in capsys.readouterr().out.splitlines() if ln.startswith("{")][-1]
+        rep = json.loads(line)
+        assert rep["vs_cv2_max_abs"] <= max_b and rep["vs_cv2_mean_abs"] <= mean_b, (kind, flag, rep)
 
 
 # ---------------------------------------------------------------- layout utilities
