@@ -70,8 +70,15 @@ def test_argument_validation():
         bb.pffft_(np.zeros((4, 4), np.uint8), 2.0)
     with pytest.raises(bb.BlurB200Error):
         bb.pocketfft_1D(np.zeros((4, 4, 3), np.float32), 2.0)
-    with pytest.raises(bb.BlurB200Error):
-        bb.Test(np.zeros((8, 8, 3), np.uint8), 1, 2.0)
+    # flag 1 = the reference's OpenCV comparison line (Source.cpp:596-603): host cv2 when importable, an error otherwise
+    try:
+        import cv2  # noqa: F401
+        img = np.full((8, 8, 3), 7, np.uint8)
+        bb.Test(img, 1, 2.0)
+        assert (img == 7).all()
+    except ImportError:
+        with pytest.raises(bb.BlurB200Error):
+            bb.Test(np.zeros((8, 8, 3), np.uint8), 1, 2.0)
 
 
 def test_every_valid_fft_length_plans_and_transforms(emu, oracle):
