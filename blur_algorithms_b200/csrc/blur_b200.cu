@@ -532,6 +532,11 @@ boxblur_v_kernel(const uint8_t* __restrict__ in, uint8_t* __restrict__ out, int 
 
 namespace blurb200 {
 void note_launches(uint64_t n) { g_launches += n; }
+// other TUs (layout_typed.cu) report their CUDA errors through blur_b200_last_cuda_error too
+__attribute__((visibility("hidden"))) void set_cuda_error(const char* what, cudaError_t e)
+{
+    g_cuda_err = std::string(what) + ": " + cudaGetErrorString(e);
+}
 }
 
 // ------------------------------------------------------------------ plan
