@@ -64,6 +64,12 @@ def _load() -> C.CDLL:
         "blur_b200_deinterleave_u8_f32_host": (i32, [vp, vp, vp, vp, u32]),
         "blur_b200_interleave_f32_u8_host": (i32, [vp, vp, vp, vp, u32]),
         "blur_b200_flip_block_f32_host": (i32, [vp, vp, i32, i32]),
+        "blur_b200_deinterleave_typed": (i32, [vp, vp, vp, vp, u32, i32, i32, vp]),
+        "blur_b200_interleave_typed": (i32, [vp, vp, vp, vp, u32, i32, i32, vp]),
+        "blur_b200_flip_block_pixels": (i32, [vp, vp, i32, i32, i32, vp]),
+        "blur_b200_deinterleave_typed_host": (i32, [vp, vp, vp, vp, u32, i32, i32]),
+        "blur_b200_interleave_typed_host": (i32, [vp, vp, vp, vp, u32, i32, i32]),
+        "blur_b200_flip_block_pixels_host": (i32, [vp, vp, i32, i32, i32]),
         "blur_b200_dft_image_device": (i32, [vp, vp, i32, i32, f64, vp, pi32, vp]),
         "blur_b200_dft_image_host": (i32, [vp, vp, i32, i32, f64, vp, pi32]),
         "blur_b200_dft_image_sizes": (i32, [i32, i32, f64, pi32, pi32]),
@@ -87,6 +93,8 @@ EXPORTED = [
     "blur_b200_fastboxblur", "blur_b200_fastboxblur_batch_host", "blur_b200_reflect_101_u8", "blur_b200_reflect_101_u8_host",
     "blur_b200_deinterleave_u8_f32", "blur_b200_interleave_f32_u8", "blur_b200_flip_block_f32",
     "blur_b200_deinterleave_u8_f32_host", "blur_b200_interleave_f32_u8_host", "blur_b200_flip_block_f32_host",
+    "blur_b200_deinterleave_typed", "blur_b200_interleave_typed", "blur_b200_flip_block_pixels",
+    "blur_b200_deinterleave_typed_host", "blur_b200_interleave_typed_host", "blur_b200_flip_block_pixels_host",
     "blur_b200_dft_image_device", "blur_b200_dft_image_host", "blur_b200_dft_image_sizes",
     "blur_b200_kernel_launches",
 ]

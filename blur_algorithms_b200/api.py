@@ -234,21 +234,39 @@ def Reflect_101(image: np.ndarray, pad_top: int, pad_bottom: int, pad_left: int,
     return out if img.ndim == 3 else out[..., 0]
 
 
+_TYPE_CODES = {"torch.uint8": 0, "torch.uint16": 1, "torch.int32": 2, "torch.float32": 3,
+               "uint8": 0, "uint16": 1, "int32": 2, "float32": 3}
+
+
+def _type_code(t) -> int:
+    try:
+        return _TYPE_CODES[str(t.dtype)]
+    except KeyError:
+        raise BlurB200Error(_lib.EINVAL, f"element type {t.dtype} is not one of uint8 / uint16 / int32 / float32") from None
+
+
 def deinterleave_BGR(d_interleaved, d_planes, total: int, stream: int | None = None) -> None:
-    """deinterleave_BGR<uint8_t,float>, Utils.hpp:159-184.  d_planes: float32 CUDA tensor [3, total]."""
-    check(lib.blur_b200_deinterleave_u8_f32(_ptr(d_interleaved), _ptr(d_planes[0]), _ptr(d_planes[1]),
-                                            _ptr(d_planes[2]), total, _stream() if stream is None else stream))
+    """deinterleave_BGR<T,U>, Utils.hpp:159-184: d_planes[c][x] = (U)(d_interleaved[3x+c] + round), round = 0.5f only
+    for floating -> integral.  T, U from the tensors' dtypes (uint8 / uint16 / int32 / float32); the blur's own
+    instantiation is <uint8_t,float>.  d_planes: CUDA tensor [3, total]."""
+    check(lib.blur_b200_deinterleave_typed(_ptr(d_interleaved), _ptr(d_planes[0]), _ptr(d_planes[1]), _ptr(d_planes[2]), total,
+                                           _type_code(d_interleaved), _type_code(d_planes),
+                                           _stream() if stream is None else stream))
 
 
 def interleave_BGR(d_planes, d_interleaved, total: int, stream: int | None = None) -> None:
-    """interleave_BGR<uint8_t,float>, Utils.hpp:186-210 (+0.5f, truncation)."""
-    check(lib.blur_b200_interleave_f32_u8(_ptr(d_planes[0]), _ptr(d_planes[1]), _ptr(d_planes[2]),
-                                          _ptr(d_interleaved), total, _stream() if stream is None else stream))
+    """interleave_BGR<T,U>, Utils.hpp:186-210: d_interleaved[3x+c] = (T)(d_planes[c][x] + round) (+0.5f and
+    truncation for float -> integral)."""
+    check(lib.blur_b200_interleave_typed(_ptr(d_planes[0]), _ptr(d_planes[1]), _ptr(d_planes[2]), _ptr(d_interleaved), total,
+                                         _type_code(d_planes), _type_code(d_interleaved),
+                                         _stream() if stream is None else stream))
 
 
-def flip_block(d_in, d_out, w: int, h: int, stream: int | None = None) -> None:
-    """flip_block<float,1>(in, out, w, h): in is h x w, out is w x h (Source.cpp:540,562)."""
-    check(lib.blur_b200_flip_block_f32(_ptr(d_in), _ptr(d_out), w, h, _stream() if stream is None else stream))
+def flip_block(d_in, d_out, w: int, h: int, stream: int | None = None, channels: int = 1) -> None:
+    """flip_block<T,C>(in, out, w, h): in is h x w pixels of C elements, out is w x h (Source.cpp:540,562 call
+    it as <float,1>)."""
+    check(lib.blur_b200_flip_block_pixels(_ptr(d_in), _ptr(d_out), w, h, channels * d_in.element_size(),
+                                          _stream() if stream is None else stream))
 
 
 # ---- DFT_image ----------------------------------------------------------------------------------

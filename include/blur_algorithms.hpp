@@ -115,22 +115,38 @@ inline void Reflect_101(const T* const input, T* output, int pad_top, int pad_bo
                      "Reflect_101");
 }
 
-// Utils.hpp:159-184 / :186-210, the instantiation the blur uses (<uint8_t, float>)
-inline void deinterleave_BGR(const uint8_t* const interleaved_BGR, float** const deinterleaved_BGR, const uint32_t total_size)
+// Utils.hpp:159-184 / :186-210.  T = interleaved element type, U = plane element type, any of
+// uint8_t, uint16_t, int32_t, float; the reference's rounding rule (0.5f only when the destination is
+// integral and the source is not) is applied by the library.  <uint8_t, float> is the instantiation the
+// blur itself uses (Source.cpp:188,268,310,389,461,567).
+namespace blur_b200 {
+template <typename T> struct type_code;
+template <> struct type_code<uint8_t> { static constexpr int value = BLUR_B200_T_U8; };
+template <> struct type_code<uint16_t> { static constexpr int value = BLUR_B200_T_U16; };
+template <> struct type_code<int32_t> { static constexpr int value = BLUR_B200_T_I32; };
+template <> struct type_code<float> { static constexpr int value = BLUR_B200_T_F32; };
+}  // namespace blur_b200
+
+template <typename T, typename U>
+inline void deinterleave_BGR(const T* const interleaved_BGR, U** const deinterleaved_BGR, const uint32_t total_size)
 {
-    blur_b200::check(blur_b200_deinterleave_u8_f32_host(interleaved_BGR, deinterleaved_BGR[0], deinterleaved_BGR[1],
-                                                        deinterleaved_BGR[2], total_size), "deinterleave_BGR");
+    blur_b200::check(blur_b200_deinterleave_typed_host(interleaved_BGR, deinterleaved_BGR[0], deinterleaved_BGR[1], deinterleaved_BGR[2],
+                                                       total_size, blur_b200::type_code<T>::value, blur_b200::type_code<U>::value),
+                     "deinterleave_BGR");
 }
-inline void interleave_BGR(const float** const deinterleaved_BGR, uint8_t* const interleaved_BGR, const uint32_t total_size)
+template <typename T, typename U>
+inline void interleave_BGR(const U** const deinterleaved_BGR, T* const interleaved_BGR, const uint32_t total_size)
 {
-    blur_b200::check(blur_b200_interleave_f32_u8_host(deinterleaved_BGR[0], deinterleaved_BGR[1], deinterleaved_BGR[2],
-                                                      interleaved_BGR, total_size), "interleave_BGR");
+    blur_b200::check(blur_b200_interleave_typed_host(deinterleaved_BGR[0], deinterleaved_BGR[1], deinterleaved_BGR[2], interleaved_BGR,
+                                                     total_size, blur_b200::type_code<U>::value, blur_b200::type_code<T>::value),
+                     "interleave_BGR");
 }
 
-// flip_block<float,1>(in, out, w, h) as called at Source.cpp:367,384,540,562: in is h x w, out w x h
+// flip_block<T,C>(in, out, w, h) as called at Source.cpp:367,384,540,562 (<float,1>): in is h x w pixels of
+// C elements, out is w x h.  Any trivially copyable T with C*sizeof(T) in {1,2,3,4,6,8,12,16} bytes.
 template <typename T, int C>
 inline void flip_block(const T* in, T* out, int w, int h)
 {
-    static_assert(std::is_same<T, float>::value && C == 1, "only the <float,1> instantiation the reference uses");
-    blur_b200::check(blur_b200_flip_block_f32_host(in, out, w, h), "flip_block");
+    static_assert(std::is_trivially_copyable<T>::value, "flip_block moves raw pixels");
+    blur_b200::check(blur_b200_flip_block_pixels_host(in, out, w, h, C * static_cast<int>(sizeof(T))), "flip_block");
 }

@@ -179,6 +179,25 @@ int blur_b200_deinterleave_u8_f32_host(const uint8_t *h_in, float *h_b, float *h
 int blur_b200_interleave_f32_u8_host(const float *h_b, const float *h_g, const float *h_r, uint8_t *h_out, uint32_t total);
 int blur_b200_flip_block_f32_host(const float *h_in, float *h_out, int w, int h);
 
+/* ---- the layout templates for other element types (Utils.hpp:159-210 are templates on T and U; flip_block<T,C>) ---- */
+/* element type codes */
+enum { BLUR_B200_T_U8 = 0, BLUR_B200_T_U16 = 1, BLUR_B200_T_I32 = 2, BLUR_B200_T_F32 = 3 };
+/* deinterleave_BGR<T,U>: planes[c][x] = (U)(in[3x+c] + round), round = 0.5f iff U integral and T floating
+ * (Utils.hpp:163); in_type = T, out_type = U.  Float -> integral truncates toward zero and saturates. */
+int blur_b200_deinterleave_typed(const void *d_in, void *d_b, void *d_g, void *d_r, uint32_t total, int in_type, int out_type,
+                                 void *stream);
+/* interleave_BGR<T,U>: out[3x+c] = (T)(planes[c][x] + round), round = 0.5f iff T integral and U floating
+ * (Utils.hpp:189); plane_type = U, out_type = T. */
+int blur_b200_interleave_typed(const void *d_b, const void *d_g, const void *d_r, void *d_out, uint32_t total, int plane_type,
+                               int out_type, void *stream);
+/* flip_block<T,C>(in,out,w,h) for any pixel of pixel_bytes = C*sizeof(T) in {1,2,3,4,6,8,12,16} bytes */
+int blur_b200_flip_block_pixels(const void *d_in, void *d_out, int w, int h, int pixel_bytes, void *stream);
+/* host-buffer forms (H2D + kernel + D2H) */
+int blur_b200_deinterleave_typed_host(const void *h_in, void *h_b, void *h_g, void *h_r, uint32_t total, int in_type, int out_type);
+int blur_b200_interleave_typed_host(const void *h_b, const void *h_g, const void *h_r, void *h_out, uint32_t total, int plane_type,
+                                    int out_type);
+int blur_b200_flip_block_pixels_host(const void *h_in, void *h_out, int w, int h, int pixel_bytes);
+
 /* ---- DFT_image spectrum path (pocketfft_2D with #define DFT_image, Source.cpp:240-252) ------- */
 /* d_in uint8 [rows][cols][3]; d_out uint8 [rows][cols][3] spectrum image; optional d_spec_f32
  * float planar [3][H][W] of the padded size (H,W returned in padded[2]). nsmooth selects the

@@ -157,6 +157,43 @@ int main(int argc, char** argv)
         flip_block<float, 1>(pp[0], fa.data(), cols, rows);
         orc_flip_block_f32(pp[0], fb.data(), cols, rows);
         expect(fa == fb, "flip_block<float,1> bit-exact vs oracle");
+        // other instantiations of the templates (Utils.hpp:159-210): <uint16_t,float>, <float,float>, <uint8_t,uint16_t>
+        {
+            std::vector<uint16_t> w16(img.size()), back16(img.size());
+            for (size_t i = 0; i < img.size(); ++i) w16[i] = static_cast<uint16_t>(img[i] * 257u);
+            deinterleave_BGR<uint16_t, float>(w16.data(), pp, total);
+            bool ok = true;
+            for (uint32_t x = 0; x < total && ok; ++x)
+                for (int c = 0; c < 3; ++c) ok = ok && pp[c][x] == static_cast<float>(w16[3 * size_t(x) + c]);       // round = 0
+            expect(ok, "deinterleave_BGR<uint16_t,float> exact");
+            for (auto& v : p) v += 0.4f;
+            interleave_BGR<uint16_t, float>(cp, back16.data(), total);
+            ok = true;
+            for (uint32_t x = 0; x < total && ok; ++x)
+                for (int c = 0; c < 3; ++c) ok = ok && back16[3 * size_t(x) + c] == static_cast<uint16_t>(pp[c][x] + 0.5f);   // Utils.hpp:189
+            expect(ok, "interleave_BGR<uint16_t,float> = (uint16_t)(v + 0.5f)");
+            std::vector<float> fi(img.size()), fo2(img.size());
+            for (size_t i = 0; i < img.size(); ++i) fi[i] = img[i] * 0.37f - 3.f;
+            std::vector<float> pl(3 * size_t(total));
+            float* plp[3] = {pl.data(), pl.data() + total, pl.data() + 2 * size_t(total)};
+            deinterleave_BGR<float, float>(fi.data(), plp, total);
+            const float* cpl[3] = {plp[0], plp[1], plp[2]};
+            interleave_BGR<float, float>(cpl, fo2.data(), total);
+            expect(fi == fo2, "deinterleave/interleave_BGR<float,float> round trip is the identity (round = 0)");
+            std::vector<uint16_t> p16(3 * size_t(total));
+            uint16_t* p16p[3] = {p16.data(), p16.data() + total, p16.data() + 2 * size_t(total)};
+            deinterleave_BGR<uint8_t, uint16_t>(img.data(), p16p, total);
+            ok = true;
+            for (uint32_t x = 0; x < total && ok; ++x)
+                for (int c = 0; c < 3; ++c) ok = ok && p16p[c][x] == img[3 * size_t(x) + c];
+            expect(ok, "deinterleave_BGR<uint8_t,uint16_t> exact (integral -> integral adds nothing)");
+            std::vector<uint8_t> t3(img.size()), t3b(img.size());
+            flip_block<uint8_t, 3>(img.data(), t3.data(), cols, rows);
+            ok = true;
+            for (int y = 0; y < rows && ok; ++y)
+                for (int x = 0; x < cols && ok; ++x) ok = !std::memcmp(&t3[(size_t(x) * rows + y) * 3], &img[(size_t(y) * cols + x) * 3], 3);
+            expect(ok, "flip_block<uint8_t,3> transposes whole pixels");
+        }
     }
     {   // error behaviour: pad > min(rows, cols) - 1 is refused, not read out of bounds
         std::vector<uint8_t> tiny = synth(8, 400, 3);

@@ -485,6 +485,42 @@ def test_deinterleave_interleave_flip(bb, oracle, torch):
     assert torch.equal(t, a.t().contiguous())
 
 
+@pytest.mark.gpu
+def test_layout_templates_other_types(bb, torch):
+    """deinterleave_BGR<T,U> / interleave_BGR<T,U> / flip_block<T,C> beyond <uint8_t,float> (Utils.hpp:159-210 are
+    templates): round = 0.5f only for floating -> integral, otherwise the value is copied."""
+    rng = np.random.default_rng(3)
+    total = 4099                                           # not a multiple of the 4-pixel groups
+    u16 = torch.from_numpy(rng.integers(0, 65536, 3 * total, dtype=np.uint16)).cuda()
+    pf = torch.empty((3, total), dtype=torch.float32, device="cuda")
+    bb.deinterleave_BGR(u16, pf, total)
+    want = u16.cpu().numpy().reshape(total, 3).T.astype(np.float32)
+    assert np.array_equal(pf.cpu().numpy(), want)
+    pf += 0.4
+    back = torch.empty_like(u16)
+    bb.interleave_BGR(pf, back, total)
+    want16 = (pf.cpu().numpy() + np.float32(0.5)).astype(np.uint16).T.reshape(-1)       # (uint16_t)(v + 0.5f), Utils.hpp:189
+    assert np.array_equal(back.cpu().numpy(), want16)
+    f = torch.from_numpy((rng.standard_normal(3 * total) * 100).astype(np.float32)).cuda()
+    pff = torch.empty((3, total), dtype=torch.float32, device="cuda")
+    bb.deinterleave_BGR(f, pff, total)
+    back_f = torch.empty_like(f)
+    bb.interleave_BGR(pff, back_f, total)
+    assert torch.equal(back_f, f)                          # <float,float>: round = 0 both ways
+    u8 = torch.from_numpy(rng.integers(0, 256, 3 * total, dtype=np.uint8)).cuda()
+    p16 = torch.empty((3, total), dtype=torch.uint16, device="cuda")
+    bb.deinterleave_BGR(u8, p16, total)
+    assert np.array_equal(p16.cpu().numpy(), u8.cpu().numpy().reshape(total, 3).T.astype(np.uint16))
+    neg = torch.tensor([[-3.2, 70000.0, 12.5]] * 3, dtype=torch.float32, device="cuda")
+    o8 = torch.empty(9, dtype=torch.uint8, device="cuda")
+    bb.interleave_BGR(neg, o8, 3)
+    assert o8.cpu().tolist() == [0, 0, 0, 255, 255, 255, 13, 13, 13]                    # saturation (undefined in the reference)
+    img = torch.from_numpy(synth("noise", 37, 53, 4)).cuda()
+    t = torch.empty((53, 37, 3), dtype=torch.uint8, device="cuda")
+    bb.flip_block(img, t, 53, 37, channels=3)
+    assert torch.equal(t, img.permute(1, 0, 2).contiguous())
+
+
 # ---------------------------------------------------------------- DFT_image
 
 def test_dft_image_vs_oracle_and_golden(bb, oracle):
