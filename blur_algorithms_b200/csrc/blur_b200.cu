@@ -744,8 +744,12 @@ int plan_create_impl(blur_b200_plan* p, const GaussGeometry& gg, int rows, int c
 }
 
 // row / column FFT kernels of an overlap-save plan: two-factor (ols2) or three-factor instantiation
-cudaError_t launch_row_fft(blur_b200_plan* p, const OlsRowIO& io, int num_sms, cudaStream_t st)
+cudaError_t launch_row_fft(blur_b200_plan* p, const OlsRowIO& io_in, int num_sms, cudaStream_t st)
 {
+    OlsRowIO io = io_in;
+    // unit order of the two-factor row grid (OlsRowIO::pair_major); BLUR_B200_ROW_ORDER=0/1 forces it (A/B measurements)
+    static const int order_env = std::getenv("BLUR_B200_ROW_ORDER") ? std::atoi(std::getenv("BLUR_B200_ROW_ORDER")) : -1;
+    io.pair_major = order_env >= 0 ? order_env : (io.peer ? 1 : 0);
     if (io.ax.R2) return launch_ols2_row(io, p->d_ols2_tw, p->d_ols2_kt, num_sms, st);
     return launch_ols_row(io, p->d_ols_twa_row, p->d_ols_twb, p->d_ols_kt_row, num_sms, st);
 }

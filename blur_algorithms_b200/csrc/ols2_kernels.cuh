@@ -161,18 +161,23 @@ ols2_row_kernel(const __grid_constant__ OlsRowIO io, const float2* __restrict__ 
     cplx w[R2];
     ols2_load_twiddles<R2>(w, reinterpret_cast<const cplx*>(tw2_), lane);
     for (int i = threadIdx.x; i < ols2_len<R2>(); i += 32 * kOls2RowWarps) kts[i] = kt[i];
-    // unit = b * npairs + pair, walked with stride nw: (pair, b) advance without divisions
-    const int nw = gridDim.x * kOls2RowWarps, npairs = io.npairs;
-    const int dpair = nw % npairs, db = nw / npairs;
+    // unit = b * npairs + pair (block-major) or pair * nblocks + b (pair-major), walked with stride nw:
+    // (pair, b) advance without divisions.  (lo, hi) = (pair, b) or (b, pair); nlo = npairs or nblocks.
+    const int nw = gridDim.x * kOls2RowWarps;
+    const bool pm = io.pair_major != 0;
+    const int nlo = pm ? io.ax.nblocks : io.npairs;
+    const int dlo = nw % nlo, dhi = nw / nlo;
     int unit = blockIdx.x * kOls2RowWarps + warp;
-    int pair = unit % npairs, b = unit / npairs;
+    int lo = unit % nlo, hi = unit / nlo;
+    int pair = pm ? hi : lo, b = pm ? lo : hi;
     if (unit < io.nunits) ols2_row_stage<R2>(io, pair, b, raw, lane);
     cp_async_commit();
     __syncthreads();                                   // the multiplier table; the only block-wide barrier
     for (; unit < io.nunits; unit += nw) {
         const OlsRowIO::Ctx ctx = io.begin(pair, b, raw, ols2_raw_pitch<R2>());
-        int npair = pair + dpair, nb = b + db;
-        if (npair >= npairs) { npair -= npairs; ++nb; }
+        int nlo_ = lo + dlo, nhi_ = hi + dhi;
+        if (nlo_ >= nlo) { nlo_ -= nlo; ++nhi_; }
+        const int npair = pm ? nhi_ : nlo_, nb = pm ? nlo_ : nhi_;
         cp_async_wait_all();
         __syncwarp();
         if (!ctx.interior) {
@@ -204,7 +209,7 @@ ols2_row_kernel(const __grid_constant__ OlsRowIO io, const float2* __restrict__ 
                 ols2_row_pass3<R2, SHARDED>(tile, io, ctx, ch, lane, w);
             // non-bulk: no barrier, the next pass 1 of this lane writes exactly the slots it has just read
         }
-        pair = npair; b = nb;
+        pair = npair; b = nb; lo = nlo_; hi = nhi_;
     }
     if (BULK) bulk_wait_all();                          // the last copies have left shared memory and are performed
 }

@@ -229,6 +229,11 @@ struct OlsRowIO {
     static constexpr int kMaxPeers = 8;
     float* qpeer[kMaxPeers];
     int rank, peer;
+    // Order in which the persistent two-factor row grid walks its (pair, block) units: 0 = block-major
+    // (unit = b * npairs + pair), 1 = pair-major (unit = pair * nblocks + b: the blocks of one row pair —
+    // i.e. all destination parts of a sharded plan — are produced together, so the peer traffic of the
+    // fused exchange is spread evenly over all links for the whole kernel).
+    int pair_major;
     // pffft Nyquist quirk (Source.cpp:414-427) on top of the exact blocks: the reference's result is
     // exact + c * (-1)^x * A with A = alternating sum of the reflect-padded line;
     // corr[ch * corr_pitch + line] = c * A, added in the epilogue.  nullptr = exact mode.

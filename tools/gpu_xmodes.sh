@@ -27,3 +27,9 @@ import sys,json
 for l in sys.stdin:
     d=json.loads(l); print('box_c5 N=$n', 'ms/step', round(d['ms_per_step'],3), 'Mpx/s', round(d['value']), 'e2e Mpx/s', round(d['e2e']['value']), 'verified', d['verified']['ok'])"
 done
+# occupancy variants of the two FFT kernels (tools/build_variant.sh), single GPU
+for v in r2c2; do
+  [ -f blur_algorithms_b200/variants/libblur_b200_$v.so ] || continue
+  echo "variant $v:"; BLUR_B200_LIB=$PWD/blur_algorithms_b200/variants/libblur_b200_$v.so timeout 300 python tools/diag/pass_time.py --variants "OLS2=1" 2>&1 | tail -1
+done
+echo "stock:"; timeout 300 python tools/diag/pass_time.py --variants "OLS2=1" 2>&1 | tail -1
