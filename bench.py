@@ -423,7 +423,7 @@ def main() -> None:
             pass_px = npx
             del q, oc
         else:
-            row_ms, colil_ms = time_passes(sb.row_pass_only, lambda: sb.plan.col_pass(sb.q_recv, sb.out_cols))
+            row_ms, colil_ms = time_passes(sb.row_pass_only, sb.col_pass_only)
             pass_px = sb.geom.valid_rows * cols
         algo = plan.info["algo"]
         two = plan.info["ols_L_row"] == 1024 and algo == 1

@@ -186,6 +186,26 @@ class GaussPlan:
     def col_pass(self, d_q_chunks, d_out_cols, stream: int | None = None):
         check(lib.blur_b200_gauss_col_pass(self._h, _ptr(d_q_chunks), _ptr(d_out_cols), _stream() if stream is None else stream))
 
+    # staged exchange (blur_b200_gauss_row_pass_staged & co. in include/blur_b200.h)
+    def staged_supported(self, nstages: int) -> bool:
+        return lib.blur_b200_gauss_staged_supported(self._h, int(nstages)) == _lib.OK
+
+    def row_pass_staged(self, d_in_stripe, q_peer_ptrs, nstages: int, stream: int | None = None):
+        """Row pass as `nstages` launches over column sub-ranges; the copy engines push each finished
+        sub-range to its owners under the next launch."""
+        arr = (C.c_void_p * len(q_peer_ptrs))(*[int(p) for p in q_peer_ptrs])
+        check(lib.blur_b200_gauss_row_pass_staged(self._h, _ptr(d_in_stripe), arr, len(q_peer_ptrs), int(nstages),
+                                                  _stream() if stream is None else stream))
+
+    def stage_wait(self, stage: int, stream: int | None = None):
+        """`stream` waits for this rank's outgoing copies of `stage`."""
+        check(lib.blur_b200_gauss_stage_wait(self._h, int(stage), _stream() if stream is None else stream))
+
+    def col_pass_stage(self, d_q_recv, d_out_cols, stage: int, nstages: int, stream: int | None = None):
+        """Column pass + interleave of sub-range `stage` of this rank's column stripe."""
+        check(lib.blur_b200_gauss_col_pass_stage(self._h, _ptr(d_q_recv), _ptr(d_out_cols), int(stage), int(nstages),
+                                                 _stream() if stream is None else stream))
+
 
 # ---- FastBoxBlur --------------------------------------------------------------------------------
 

@@ -590,6 +590,10 @@ struct blur_b200_plan {
     cudaEvent_t ev_pushed = nullptr;
     cudaStream_t ce_stream[7] = {};                // one per destination GPU: copies to different peers run on different engines
     cudaEvent_t ev_ce[7] = {};
+    // staged exchange (blur_b200_gauss_row_pass_staged): row launch of stage k done / copy of stage k to destination d done
+    static constexpr int kMaxStages = 8;
+    cudaEvent_t ev_stage[kMaxStages] = {};
+    cudaEvent_t ev_scopy[kMaxStages][7] = {};
 };
 
 namespace {
@@ -969,6 +973,8 @@ void blur_b200_gauss_plan_destroy(blur_b200_plan* p)
     if (p->push_stream) cudaStreamDestroy(p->push_stream);
     for (cudaEvent_t e : p->ev_chunk) if (e) cudaEventDestroy(e);
     if (p->ev_pushed) cudaEventDestroy(p->ev_pushed);
+    for (cudaEvent_t e : p->ev_stage) if (e) cudaEventDestroy(e);
+    for (auto& row : p->ev_scopy) for (cudaEvent_t e : row) if (e) cudaEventDestroy(e);
     for (cudaStream_t cs : p->ce_stream) if (cs) cudaStreamDestroy(cs);
     for (cudaEvent_t e : p->ev_ce) if (e) cudaEventDestroy(e);
     delete p;
@@ -1185,7 +1191,7 @@ int blur_b200_gauss_row_pass_push(blur_b200_plan* p, const uint8_t* d_in_stripe,
         for (cudaEvent_t& e : p->ev_chunk) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
         CU_TRY(cudaEventCreateWithFlags(&p->ev_pushed, cudaEventDisableTiming));
         for (int d = 0; d + 1 < N; ++d) {
-            CU_TRY(cudaStreamCreateWithPriority(&p->ce_stream[d], cudaStreamNonBlocking, prio_hi));
+            if (!p->ce_stream[d]) CU_TRY(cudaStreamCreateWithPriority(&p->ce_stream[d], cudaStreamNonBlocking, prio_hi));
             CU_TRY(cudaEventCreateWithFlags(&p->ev_ce[d], cudaEventDisableTiming));
         }
     }
@@ -1266,6 +1272,153 @@ int blur_b200_gauss_row_pass_push(blur_b200_plan* p, const uint8_t* d_in_stripe,
             CU_TRY(cudaStreamWaitEvent(st, p->ev_ce[d], 0));
         }
     }
+    return BLUR_B200_OK;
+}
+
+// ---- staged exchange ------------------------------------------------------------------------------
+// The part of every rank (cpart columns) is cut into `nstages` sub-ranges of w = cpart / nstages columns.
+// Stage k of the row pass transforms, for all rows of the stripe, the overlap-save blocks that touch
+// sub-range k of any rank's part (and no earlier sub-range); as soon as its launch has finished the copy
+// engines move sub-range k to its owners while the next stage's FFTs run, and the column pass of
+// sub-range k starts when every rank's copies of stage k have landed — the exchange (the distributed
+// flip_block, Source.cpp:540) is hidden behind both FFT passes instead of sitting between them.
+// Buffers (send buffer of the plan and every rank's receive buffer): [stage][3][nranks][stripe_rows][w].
+namespace {
+
+int staged_check(const blur_b200_plan* p, int nstages)
+{
+    if (!p || nstages < 1 || nstages > blur_b200_plan::kMaxStages) return BLUR_B200_EINVAL;
+    if (p->algo != 1 || p->quirk_ols || !p->ols_row.R2 || !p->ols_col.R2) return BLUR_B200_ESIZE;
+    if (p->cpart % (16 * nstages) != 0) return BLUR_B200_ESIZE;            // whole octet pairs per sub-range
+    const int w = p->cpart / nstages;
+    if (p->nranks * nstages > OlsRowIO::kMaxParts || p->ols_row.nblocks > OlsRowIO::kMaxSel) return BLUR_B200_ESIZE;
+    // bulk epilogue of the row kernel: 16-byte aligned pieces, a block spans at most kOls2BulkPieces sub-ranges
+    if (p->ols_row.V % 4 != 0 || p->cols % 4 != 0 || p->ols_row.V > 3 * w) return BLUR_B200_ESIZE;
+    return BLUR_B200_OK;
+}
+
+// blocks of stage k: a block belongs to the earliest sub-range index (column / w) % nstages it touches
+void stage_blocks(const blur_b200_plan* p, int nstages, int k, unsigned char* sel, int& n)
+{
+    const int w = p->cpart / nstages, V = p->ols_row.V;
+    n = 0;
+    for (int b = 0; b < p->ols_row.nblocks; ++b) {
+        const int x0 = b * V, x1 = std::min(p->cols, x0 + V) - 1;
+        const int v0 = x0 / w, v1 = x1 / w;
+        const int st = (v1 - v0 + 1 >= nstages || v0 % nstages + (v1 - v0) >= nstages) ? 0 : v0 % nstages;
+        if (st == k) sel[n++] = static_cast<unsigned char>(b);
+    }
+}
+
+}  // namespace
+
+int blur_b200_gauss_staged_supported(const blur_b200_plan* p, int nstages) { return staged_check(p, nstages); }
+
+int blur_b200_gauss_row_pass_staged(blur_b200_plan* p, const uint8_t* d_in_stripe, float* const* q_peers, int npeers,
+                                    int nstages, void* stream)
+{
+    if (!p || !d_in_stripe || !q_peers || npeers != p->nranks || npeers > OlsRowIO::kMaxPeers) return BLUR_B200_EINVAL;
+    int rc = staged_check(p, nstages);
+    if (rc) return rc;
+    for (int k = 0; k < npeers; ++k)
+        if (!q_peers[k]) return BLUR_B200_EINVAL;
+    if (p->valid_rows <= 0) return BLUR_B200_OK;
+    CU_TRY(cudaSetDevice(p->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int N = p->nranks, rank = p->rank, S = nstages;
+    if (!p->ev_stage[0]) {
+        int prio_lo = 0, prio_hi = 0;
+        CU_TRY(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
+        for (int k = 0; k < blur_b200_plan::kMaxStages; ++k) {
+            CU_TRY(cudaEventCreateWithFlags(&p->ev_stage[k], cudaEventDisableTiming));
+            for (int d = 0; d < 7; ++d) CU_TRY(cudaEventCreateWithFlags(&p->ev_scopy[k][d], cudaEventDisableTiming));
+        }
+        for (int d = 0; d + 1 < N; ++d)
+            if (!p->ce_stream[d]) CU_TRY(cudaStreamCreateWithPriority(&p->ce_stream[d], cudaStreamNonBlocking, prio_hi));
+    }
+    const int w = p->cpart / S;
+    const size_t blk = static_cast<size_t>(p->stripe_rows) * w;            // floats per (stage, channel, source) block
+    const size_t plane = static_cast<size_t>(3) * N * blk;                 // floats per stage
+    for (int k = 0; k < S; ++k) {
+        OlsRowIO io{};
+        io.in = d_in_stripe; io.q = p->d_q;
+        io.rows = p->valid_rows; io.cols = p->cols;
+        io.npairs = cdiv(p->valid_rows, 2);
+        io.srows = p->stripe_rows; io.qpitch = w; io.cpart = w; io.nparts = N * S; io.chparts = N;
+        io.ax = p->ols_row;
+        io.peer = 1; io.rank = rank;
+        // virtual part v = (destination d, sub-range kk): own part straight into the own receive buffer, the others
+        // into the send buffer at the source-block slot of the destination (the kernel adds rank * blk)
+        for (int d = 0; d < N; ++d)
+            for (int kk = 0; kk < S; ++kk)
+                io.qpeer[d * S + kk] = d == rank ? q_peers[rank] + kk * plane
+                                                 : p->d_q + kk * plane + (static_cast<ptrdiff_t>(d) - rank) * static_cast<ptrdiff_t>(blk);
+        stage_blocks(p, S, k, io.bsel, io.nbsel);
+        io.nunits = io.nbsel * io.npairs;
+        if (io.nbsel > 0) {
+            CU_TRY(launch_row_fft(p, io, p->num_sms, st));
+            ++g_launches;
+        }
+        if (N == 1) continue;
+        CU_TRY(cudaEventRecord(p->ev_stage[k], st));
+        const size_t width = static_cast<size_t>(p->valid_rows) * w * sizeof(float);
+        const size_t pitch = static_cast<size_t>(N) * blk * sizeof(float);
+        for (int di = 0; di + 1 < N; ++di) {                    // start with the next rank: spread the NVSwitch ports
+            const int d = (rank + 1 + di) % N;
+            cudaStream_t cs = p->ce_stream[di];
+            CU_TRY(cudaStreamWaitEvent(cs, p->ev_stage[k], 0));
+            CU_TRY(cudaMemcpy2DAsync(q_peers[d] + k * plane + static_cast<size_t>(rank) * blk, pitch,
+                                     p->d_q + k * plane + static_cast<size_t>(d) * blk, pitch, width, 3, cudaMemcpyDeviceToDevice, cs));
+            CU_TRY(cudaEventRecord(p->ev_scopy[k][di], cs));
+        }
+    }
+    return BLUR_B200_OK;
+}
+
+int blur_b200_gauss_stage_wait(blur_b200_plan* p, int stage, void* stream)
+{
+    if (!p || stage < 0 || stage >= blur_b200_plan::kMaxStages) return BLUR_B200_EINVAL;
+    if (p->valid_rows <= 0 || p->nranks == 1 || !p->ev_stage[0]) return BLUR_B200_OK;
+    CU_TRY(cudaSetDevice(p->device));
+    for (int di = 0; di + 1 < p->nranks; ++di) CU_TRY(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), p->ev_scopy[stage][di], 0));
+    return BLUR_B200_OK;
+}
+
+int blur_b200_gauss_col_pass_stage(blur_b200_plan* p, const float* d_q_recv, uint8_t* d_out_cols, int stage, int nstages, void* stream)
+{
+    if (!p || !d_q_recv || !d_out_cols || stage < 0 || stage >= nstages) return BLUR_B200_EINVAL;
+    int rc = staged_check(p, nstages);
+    if (rc) return rc;
+    CU_TRY(cudaSetDevice(p->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int N = p->nranks, S = nstages, w = p->cpart / S;
+    const int noct_total = std::min(p->qpitch / 8, cdiv(std::max(0, p->cols - p->rank * p->cpart), 8));
+    const int noct = std::max(0, std::min(w / 8, noct_total - stage * (w / 8)));
+    if (noct <= 0) return BLUR_B200_OK;
+    const size_t blk = static_cast<size_t>(p->stripe_rows) * w;
+    const size_t plane = static_cast<size_t>(3) * N * blk;
+    uint8_t* u = p->d_u + static_cast<size_t>(stage) * 3 * (w / 8) * p->rows * 8;       // [3][noct][rows][8] of this sub-range
+    OlsColIO io{};
+    io.u = u;
+    io.rows = p->rows;
+    io.noct = noct;
+    io.ax = p->ols_col;
+    io.b0 = 0;
+    io.nbl = io.ax.nblocks;
+    io.nunits = ols2_col_npairs(io.noct, io.nbl);
+    CU_TRY(launch_ols2_col(io, d_q_recv + stage * plane, w, N * p->stripe_rows, p->d_ols2_tw, p->d_ols2_kt, p->num_sms, st));
+    ++g_launches;
+    const int out_cols = 2 * p->cpp;
+    const int valid_cols = std::max(0, std::min(p->cpart, p->cols - p->rank * p->cpart));
+    const int ncols = std::max(0, std::min(w, valid_cols - stage * w));
+    if (ncols <= 0) return BLUR_B200_OK;
+    uint8_t* out = d_out_cols + static_cast<size_t>(stage) * w * 3;
+    const int vec = (static_cast<size_t>(out_cols) * 3 % 16 == 0) && (reinterpret_cast<uintptr_t>(out) % 16 == 0) &&
+                    (reinterpret_cast<uintptr_t>(u) % 32 == 0) && (p->rows % 4 == 0);
+    dim3 g(cdiv(cdiv(noct, 2), 32), cdiv(cdiv(p->rows, 4), 8));
+    interleave_oct_kernel<<<g, dim3(32, 8), 0, st>>>(u, out, p->rows, noct, std::min(ncols, noct * 8), out_cols, vec, 0, p->rows);
+    CU_TRY(cudaGetLastError());
+    ++g_launches;
     return BLUR_B200_OK;
 }
 

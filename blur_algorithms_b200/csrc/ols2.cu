@@ -25,8 +25,8 @@ cudaError_t launch_ols2_row(const OlsRowIO& io, const float2* tw2, const float* 
     // bulk epilogue: every piece a bulk copy moves must be 16-byte aligned at both ends
     static const int bulk_env = std::getenv("BLUR_B200_ROW_BULK") ? std::atoi(std::getenv("BLUR_B200_ROW_BULK")) : -1;
     const int cpart = sharded ? io.cpart : io.qpitch;
-    bool bulk = io.ax.V % 4 == 0 && io.cols % 4 == 0 && io.qpitch % 4 == 0 && cpart % 4 == 0 && io.ax.V <= cpart &&
-                reinterpret_cast<uintptr_t>(io.q) % 16 == 0;
+    bool bulk = io.ax.V % 4 == 0 && io.cols % 4 == 0 && io.qpitch % 4 == 0 && cpart % 4 == 0 &&
+                io.ax.V <= (kOls2BulkPieces - 1) * cpart && reinterpret_cast<uintptr_t>(io.q) % 16 == 0;
     for (int k = 0; bulk && sharded && io.peer && k < io.nparts; ++k) bulk = reinterpret_cast<uintptr_t>(io.qpeer[k]) % 16 == 0;
     if (bulk_env == 0) bulk = false;
     const void* fn = sharded ? (bulk ? (const void*)ols2_row_kernel<R2, true, true> : (const void*)ols2_row_kernel<R2, true, false>)

@@ -150,6 +150,7 @@ BLUR_HD void ols2_row_pass3(const cplx* __restrict__ tile, const OlsRowIO& io, c
     const uint32_t keep = ols2_item_mask<R2>(n2, io.ax.halo, c.nvalid);
     const int x0 = c.s + n2;
     const int nparts = SHARDED ? io.nparts : 1, qpitch = io.qpitch;
+    const int chparts = SHARDED && io.chparts ? io.chparts : nparts;       // source blocks per channel plane of a peer buffer
     float* qc = c.qa + static_cast<size_t>(ch) * nparts * io.srows * qpitch;
     if (!SHARDED) {
         float* d = qc + x0;
@@ -164,7 +165,7 @@ BLUR_HD void ols2_row_pass3(const cplx* __restrict__ tile, const OlsRowIO& io, c
         }
     } else if (io.ax.V <= 2 * io.cpart) {
         // the block's outputs span at most three parts: three base pointers, then a select per element
-        const size_t rowoff = io.peer ? (static_cast<size_t>(ch * nparts + io.rank) * io.srows + c.ra) * qpitch : 0;
+        const size_t rowoff = io.peer ? (static_cast<size_t>(ch * chparts + io.rank) * io.srows + c.ra) * qpitch : 0;
         float* pp[3];
 #pragma unroll
         for (int k = 0; k < 3; ++k) {
@@ -186,7 +187,7 @@ BLUR_HD void ols2_row_pass3(const cplx* __restrict__ tile, const OlsRowIO& io, c
             const bool va = keep >> j & 1u, vb = va && c.has_b;
             const int xx = va ? x0 + R2 * j : 0;
             const int part = xx / io.cpart;
-            float* d = io.peer ? io.qpeer[part] + (static_cast<size_t>(ch * nparts + io.rank) * io.srows + c.ra) * qpitch + (xx - part * io.cpart)
+            float* d = io.peer ? io.qpeer[part] + (static_cast<size_t>(ch * chparts + io.rank) * io.srows + c.ra) * qpitch + (xx - part * io.cpart)
                                : qc + static_cast<size_t>(part) * io.srows * qpitch + (xx - part * io.cpart);
             if (va) d[0] = cre(x[j]);
             if (vb) d[qpitch] = cim(x[j]);

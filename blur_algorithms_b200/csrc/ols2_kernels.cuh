@@ -93,6 +93,7 @@ __device__ __forceinline__ void bulk_wait_read() { asm volatile("cp.async.bulk.w
 __device__ __forceinline__ void bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 
 constexpr int kOls2BulkB = 1056;       // float offset of line b's outputs in the tile (tile = 2112 floats)
+constexpr int kOls2BulkPieces = 4;     // parts one block's outputs may span in the bulk epilogue
 
 template <int R2, bool SHARDED>
 __device__ __forceinline__ void ols2_row_pass3_bulk(cplx* __restrict__ tile, const OlsRowIO& io, const OlsRowIO::Ctx& c, int ch,
@@ -118,28 +119,30 @@ __device__ __forceinline__ void ols2_row_pass3_bulk(cplx* __restrict__ tile, con
         if (keep >> j & 1u) { oa[R2 * j] = cre(x[j]); oa[kOls2BulkB + R2 * j] = cim(x[j]); }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
     __syncwarp();
-    // lane = 2 * line + segment
-    const int line = lane >> 1, seg = lane & 1;
-    if (lane < 4 && (line == 0 || c.has_b)) {
+    // lane = 2 * piece + line: piece p is the run of kept columns that falls into part part0 + p (a block spans
+    // at most kOls2BulkPieces parts: the launcher checks V <= (kOls2BulkPieces - 1) * cpart)
+    const int line = lane & 1, piece = lane >> 1;
+    if (lane < 2 * kOls2BulkPieces && (line == 0 || c.has_b)) {
         const int x_start = c.s + io.ax.halo;           // first kept column of the block
         const int nparts = SHARDED ? io.nparts : 1;
-        int o0 = 0, n = c.nvalid, part = 0;
+        const int part = SHARDED ? c.part0 + piece : 0;
+        int x0 = x_start, x1 = x_start + c.nvalid;
         if (SHARDED) {
-            part = c.part0;
-            const int n0 = min(c.nvalid, c.b1 - x_start);       // columns that stay in part0
-            if (seg == 0) n = n0; else { o0 = n0; n = c.nvalid - n0; ++part; }
-        } else if (seg) {
-            n = 0;
+            x0 = max(x0, part * io.cpart);
+            x1 = min(x1, (part + 1) * io.cpart);
+        } else if (piece) {
+            x1 = x0;
         }
-        if (n > 0) {
-            const int xx = x_start + o0;
+        if (x1 > x0 && part < nparts) {
             float* d;
-            if (SHARDED && io.peer)
-                d = io.qpeer[part] + (static_cast<size_t>(ch * nparts + io.rank) * io.srows + c.ra + line) * io.qpitch + (xx - part * io.cpart);
-            else
+            if (SHARDED && io.peer) {
+                const int chparts = io.chparts ? io.chparts : nparts;
+                d = io.qpeer[part] + (static_cast<size_t>(ch * chparts + io.rank) * io.srows + c.ra + line) * io.qpitch + (x0 - part * io.cpart);
+            } else {
                 d = c.qa + (static_cast<size_t>(ch) * nparts + part) * io.srows * io.qpitch + static_cast<size_t>(line) * io.qpitch +
-                    (xx - part * io.cpart);
-            bulk_store(d, reinterpret_cast<const float*>(tile) + line * kOls2BulkB + o0, static_cast<uint32_t>(n) * 4u);
+                    (x0 - part * io.cpart);
+            }
+            bulk_store(d, reinterpret_cast<const float*>(tile) + line * kOls2BulkB + (x0 - x_start), static_cast<uint32_t>(x1 - x0) * 4u);
         }
     }
     bulk_commit();
@@ -161,20 +164,26 @@ ols2_row_kernel(const __grid_constant__ OlsRowIO io, const float2* __restrict__ 
     cplx w[R2];
     ols2_load_twiddles<R2>(w, reinterpret_cast<const cplx*>(tw2_), lane);
     for (int i = threadIdx.x; i < ols2_len<R2>(); i += 32 * kOls2RowWarps) kts[i] = kt[i];
-    // unit = b * npairs + pair (block-major) or pair * nblocks + b (pair-major), walked with stride nw:
-    // (pair, b) advance without divisions.  (lo, hi) = (pair, b) or (b, pair); nlo = npairs or nblocks.
+    // unit = b * npairs + pair (block-major), walked with stride nw, or unit = pair * nblocks + b (pair-major),
+    // every warp a contiguous run of units (a stride would pin a warp to one block index whenever nw is a
+    // multiple of nblocks, and the edge blocks with their reflect fix-ups would always hit the same warps).
+    // (lo, hi) = (pair, b) or (b, pair); nlo = npairs or nblocks; both orders advance without divisions.
     const int nw = gridDim.x * kOls2RowWarps;
     const bool pm = io.pair_major != 0;
-    const int nlo = pm ? io.ax.nblocks : io.npairs;
-    const int dlo = nw % nlo, dhi = nw / nlo;
-    int unit = blockIdx.x * kOls2RowWarps + warp;
+    const int nblk = io.nbsel ? io.nbsel : io.ax.nblocks;        // blocks this launch transforms (OlsRowIO::bsel)
+    const int nlo = pm ? nblk : io.npairs;
+    const int wid = blockIdx.x * kOls2RowWarps + warp;
+    const int step = pm ? 1 : nw;
+    const int dlo = step % nlo, dhi = step / nlo;
+    int unit = pm ? static_cast<int>(static_cast<long long>(io.nunits) * wid / nw) : wid;
+    const int uend = pm ? static_cast<int>(static_cast<long long>(io.nunits) * (wid + 1) / nw) : io.nunits;
     int lo = unit % nlo, hi = unit / nlo;
     int pair = pm ? hi : lo, b = pm ? lo : hi;
-    if (unit < io.nunits) ols2_row_stage<R2>(io, pair, b, raw, lane);
+    if (unit < uend) ols2_row_stage<R2>(io, pair, io.nbsel ? io.bsel[b] : b, raw, lane);
     cp_async_commit();
     __syncthreads();                                   // the multiplier table; the only block-wide barrier
-    for (; unit < io.nunits; unit += nw) {
-        const OlsRowIO::Ctx ctx = io.begin(pair, b, raw, ols2_raw_pitch<R2>());
+    for (; unit < uend; unit += step) {
+        const OlsRowIO::Ctx ctx = io.begin(pair, io.nbsel ? io.bsel[b] : b, raw, ols2_raw_pitch<R2>());
         int nlo_ = lo + dlo, nhi_ = hi + dhi;
         if (nlo_ >= nlo) { nlo_ -= nlo; ++nhi_; }
         const int npair = pm ? nhi_ : nlo_, nb = pm ? nlo_ : nhi_;
@@ -198,7 +207,7 @@ ols2_row_kernel(const __grid_constant__ OlsRowIO io, const float2* __restrict__ 
             __syncwarp();
             if (ch == 2) {
                 // the staged bytes are consumed: fetch the next unit's underneath passes 2 and 3
-                if (unit + nw < io.nunits) ols2_row_stage<R2>(io, npair, nb, raw, lane);
+                if (unit + step < uend) ols2_row_stage<R2>(io, npair, io.nbsel ? io.bsel[nb] : nb, raw, lane);
                 cp_async_commit();
             }
             ols2_pass2<R2, 1>(tile, lane, w, kts);

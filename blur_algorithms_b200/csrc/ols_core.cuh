@@ -226,9 +226,19 @@ struct OlsRowIO {
     // Q buffer of the GPU that owns its column, qpeer[part], over NVLink peer mappings, as block
     // `rank` of that buffer ([3][nparts][srows][qpitch], block index = source rank): the
     // distributed flip_block (Source.cpp:540) costs no pass over HBM and no collective call.
+    // Staged exchange: every rank's part is cut into column sub-ranges ("stages"), so nparts = ranks x stages
+    // virtual parts of cpart columns each, qpeer[v] = base of virtual part v's buffer, and a channel plane of
+    // such a buffer holds `chparts` (= ranks) source blocks: address = qpeer[v] + ((ch * chparts + rank) * srows
+    // + row) * qpitch + column within the part.  chparts = 0 means nparts (no stages).
     static constexpr int kMaxPeers = 8;
-    float* qpeer[kMaxPeers];
-    int rank, peer;
+    static constexpr int kMaxParts = 64;
+    float* qpeer[kMaxParts];
+    int rank, peer, chparts;
+    // Block selection (two-factor kernel): when nbsel > 0 the launch transforms only the overlap-save blocks
+    // bsel[0 .. nbsel) of every line (a stage of the staged exchange); nunits = nbsel * npairs.
+    static constexpr int kMaxSel = 64;
+    int nbsel;
+    unsigned char bsel[kMaxSel];
     // Order in which the persistent two-factor row grid walks its (pair, block) units: 0 = block-major
     // (unit = b * npairs + pair), 1 = pair-major (unit = pair * nblocks + b: the blocks of one row pair —
     // i.e. all destination parts of a sharded plan — are produced together, so the peer traffic of the

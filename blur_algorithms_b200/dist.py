@@ -4,15 +4,22 @@ Row pass on row stripes, one exchange of the float32 intermediate (the distribut
 reference's flip_block, Source.cpp:540), column pass on column stripes.  One process per GPU.
 
 On GPUs every rank's receive buffer lives in symmetric memory (torch.distributed._symmetric_memory:
-CUDA peer mappings over NVLink/NVSwitch) and no collective library call is on the data path.  Two
-exchange modes (BLUR_B200_EXCHANGE):
-  "push"  (default) the row pass runs in wave-aligned chunks of row pairs; the kernel writes this
+CUDA peer mappings over NVLink/NVSwitch) and no collective library call is on the data path.
+Exchange modes (BLUR_B200_EXCHANGE):
+  "staged" (default where the plan supports it) every rank's part is cut into column sub-ranges; the row
+          pass runs sub-range by sub-range, the copy engines push each finished sub-range to its owners
+          under the next one's FFTs, and the column pass of a sub-range starts as soon as every rank's
+          copies of it have landed (one device-side barrier per sub-range) while the later sub-ranges
+          are still on the wire: the exchange hides behind both FFT passes
+          (blur_b200_gauss_row_pass_staged / _stage_wait / _col_pass_stage);
+  "push"  the row pass runs in wave-aligned chunks of row pairs; the kernel writes this
           rank's own part into its receive buffer and the rest into a local send buffer, and as soon
           as a chunk is done the GPU's COPY ENGINES move it into the owners' buffers (one 2-D peer
           copy per destination) underneath the next chunk's FFTs (blur_b200_gauss_row_pass_push);
   "store" the row kernel's epilogue stores every result straight into the owner's buffer
-          (blur_b200_gauss_row_pass_peer): no staging, but 4-byte remote stores.
-Two device-side barriers per blur order the ranks.  Fallback (`fused=False`, or symmetric memory
+          (blur_b200_gauss_row_pass_peer; bulk shared->global copies from the two-factor kernel): no send
+          buffer, but the SMs stay busy until the last byte has crossed NVLink.
+Device-side barriers order the ranks (push / store: two per blur).  Fallback (`fused=False`, or symmetric memory
 unavailable): a local Q buffer + NCCL all_to_all.  The CPU tests run the same host logic over gloo
 with the two passes supplied as callables.
 
@@ -166,8 +173,9 @@ class ShardedGaussBlur:
         self.symm = None
         # "push": row pass in chunks + copy kernel over peer mappings (default); "store": the row
         # kernel's epilogue stores remotely itself.  BLUR_B200_EXCHANGE overrides.
-        self.exchange_mode = exchange_mode or os.environ.get("BLUR_B200_EXCHANGE", "push")
+        self.exchange_mode = exchange_mode or os.environ.get("BLUR_B200_EXCHANGE", "staged")
         self.nchunks = nchunks or int(os.environ.get("BLUR_B200_CHUNKS", "0")) or {2: 12}.get(self.nranks, 2)
+        self.nstages = int(os.environ.get("BLUR_B200_STAGES", "0")) or 4
         self.q_send = None
         want_fused = (fused is not False and row_pass is None and col_pass is None and self.nranks > 1
                       and self.nranks <= 8 and g.algo == 1 and self.device.type == "cuda")
@@ -194,6 +202,12 @@ class ShardedGaussBlur:
             row_pass = self.plan.row_pass
             col_pass = self.plan.col_pass
         self._row_pass, self._col_pass = row_pass, col_pass
+        if self.exchange_mode == "staged":
+            # fewer stages if the part does not divide, plain push if the plan cannot run staged at all
+            while self.nstages > 1 and not (self.plan is not None and self.symm is not None and self.plan.staged_supported(self.nstages)):
+                self.nstages //= 2
+            if self.plan is None or self.symm is None or not self.plan.staged_supported(self.nstages):
+                self.exchange_mode = "push"
 
     @property
     def fused(self) -> bool:
@@ -203,8 +217,13 @@ class ShardedGaussBlur:
         """What moves the float32 intermediate between the ranks (for bench.py's config line)."""
         if not self.fused:
             return "NCCL all_to_all of the float32 intermediate (local send buffer)"
+        if self.exchange_mode == "staged":
+            return (f"staged: {self.nstages} column sub-ranges per rank; row pass sub-range by sub-range, copy engines "
+                    "(cudaMemcpy2DAsync peer copies, one per destination and sub-range) push each finished sub-range into the "
+                    "owners' symmetric-memory buffers under the next one's FFTs; the column pass of a sub-range starts after a "
+                    "device-side barrier for that sub-range while later ones are still on the wire")
         if self.exchange_mode == "store":
-            return "row-kernel epilogue stores into the owners' symmetric-memory buffers over NVLink (4-byte peer stores)"
+            return "row-kernel epilogue stores into the owners' symmetric-memory buffers over NVLink (bulk shared->global copies)"
         return (f"row pass in {self.nchunks} wave-aligned chunks; copy engines (cudaMemcpy2DAsync peer copies, one per "
                 "destination and chunk) move each finished chunk from a local send buffer into the owners' "
                 "symmetric-memory buffers under the next chunk's FFTs")
@@ -215,10 +234,22 @@ class ShardedGaussBlur:
             return
         if not self.fused:
             self._row_pass(self._last_in, self.q_send)
+        elif self.exchange_mode == "staged":
+            self.plan.row_pass_staged(self._last_in, self.peer_ptrs, self.nstages)
+            for k in range(self.nstages):
+                self.plan.stage_wait(k)
         elif self.exchange_mode == "store":
             self.plan.row_pass_peer(self._last_in, self.peer_ptrs)
         else:
             self.plan.row_pass_push(self._last_in, self.peer_ptrs, self.nchunks)
+
+    def col_pass_only(self) -> None:
+        """The column phase without barriers (per-pass timing in bench.py)."""
+        if self.fused and self.exchange_mode == "staged":
+            for k in range(self.nstages):
+                self.plan.col_pass_stage(self.q_recv, self.out_cols, k, self.nstages)
+        else:
+            self._col_pass(self.q_recv, self.out_cols)
 
     def run(self, in_stripe: torch.Tensor) -> torch.Tensor:
         """in_stripe: uint8 [valid_rows, cols, 3] (this rank's rows).  Returns this rank's column
@@ -232,6 +263,10 @@ class ShardedGaussBlur:
         if self.symm is not None:
             # peers may still be reading their buffers (previous blur's column pass)
             self.symm.barrier(channel=0)
+            if self.exchange_mode == "staged":
+                if self.geom.valid_rows > 0:
+                    self.plan.row_pass_staged(in_stripe, self.peer_ptrs, self.nstages)
+                return                                   # the per-stage barriers are in _cols()
             if self.geom.valid_rows > 0:
                 if self.exchange_mode == "store":
                     self.plan.row_pass_peer(in_stripe, self.peer_ptrs)
@@ -244,7 +279,14 @@ class ShardedGaussBlur:
             exchange(self.q_send, self.q_recv, self.group, self.geom.algo)
 
     def _cols(self) -> torch.Tensor:
-        self._col_pass(self.q_recv, self.out_cols)
+        if self.symm is not None and self.exchange_mode == "staged":
+            for k in range(self.nstages):
+                if self.geom.valid_rows > 0:
+                    self.plan.stage_wait(k)              # this rank's outgoing copies of sub-range k are complete ...
+                self.symm.barrier(channel=1 + k)         # ... and so are everybody else's: sub-range k has landed here
+                self.plan.col_pass_stage(self.q_recv, self.out_cols, k, self.nstages)
+        else:
+            self._col_pass(self.q_recv, self.out_cols)
         return self.out_cols[:, : self.geom.valid_cols]
 
     def run_host_stream(self, h_ins: list, h_outs: list) -> None:

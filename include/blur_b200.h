@@ -145,6 +145,23 @@ int blur_b200_gauss_row_pass_peer(blur_b200_plan *plan, const uint8_t *d_in_stri
 int blur_b200_gauss_row_pass_push(blur_b200_plan *plan, const uint8_t *d_in_stripe, float *const *q_peers, int npeers,
                                   int nchunks, void *stream);
 
+/* Staged exchange (two-factor overlap-save plans, nranks <= 8): the exchange hidden behind BOTH FFT passes.
+ * Every rank's part (2*cpp columns) is cut into `nstages` column sub-ranges of w = 2*cpp / nstages columns.  The
+ * row pass runs as nstages launches; launch k transforms, for every row of the stripe, the overlap-save blocks that
+ * touch sub-range k of any rank's part, and as soon as it has finished the copy engines push sub-range k into the
+ * owners' receive buffers q_peers[r] while launch k+1 computes.  blur_b200_gauss_stage_wait makes `stream` wait
+ * for this rank's outgoing copies of one stage; after the caller's cross-rank barrier for that stage,
+ * blur_b200_gauss_col_pass_stage transforms and interleaves sub-range k of this rank's column stripe — while the
+ * later stages are still on the wire.  Receive-buffer layout for this mode: [stage][3][nranks][stripe_rows][w]
+ * (same size as the unstaged layout).  blur_b200_gauss_staged_supported: BLUR_B200_OK, or BLUR_B200_ESIZE when the
+ * plan / stage count cannot run staged (use blur_b200_gauss_row_pass_push then).  Replaces flip_block, Source.cpp:540. */
+int blur_b200_gauss_staged_supported(const blur_b200_plan *plan, int nstages);
+int blur_b200_gauss_row_pass_staged(blur_b200_plan *plan, const uint8_t *d_in_stripe, float *const *q_peers, int npeers,
+                                    int nstages, void *stream);
+int blur_b200_gauss_stage_wait(blur_b200_plan *plan, int stage, void *stream);
+int blur_b200_gauss_col_pass_stage(blur_b200_plan *plan, const float *d_q_recv, uint8_t *d_out_cols, int stage, int nstages,
+                                   void *stream);
+
 /* Parity hook: the float32 row-pass result (`resf` of Source.cpp:536) as planar [3][rows][cols]. */
 int blur_b200_gauss_rowpass_f32(blur_b200_plan *plan, const uint8_t *d_in, float *d_planar, void *stream);
 

@@ -275,6 +275,60 @@ def test_gauss_sharded_emulated_on_one_gpu(bb, torch):
             pl.close()
 
 
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode_name", ["staged", "peer", "push"])
+def test_gauss_sharded_exchange_modes_emulated_on_one_gpu(bb, torch, mode_name):
+    """The three fused exchange paths (staged sub-ranges, row-kernel peer stores, chunked push) with all P ranks'
+    plans in ONE process: the peer pointers are the other plans' receive buffers on the same device.  Results must
+    be bit-identical to the single-GPU plan, including ragged sizes (odd widths, parts beyond the image, last rank
+    with fewer rows)."""
+    cases = [(1080, 4096, 50.0, 2, 4), (2160, 3840, 25.0, 2, 2), (700, 4096, 30.0, 4, 2), (333, 8192, 50.0, 8, 2),
+             (1001, 1531, 9.0, 4, 2), (600, 8192, 50.0, 8, 4), (900, 1500, 50.0, 2, 2)]
+    ran = 0
+    for rows, cols, sigma, P, S in cases:
+        img = synth("noise", rows, cols, 11)
+        single = torch.from_numpy(img).cuda()
+        p1 = bb.GaussPlan(rows, cols, sigma, 0)
+        p1.run(single)
+        plans = [bb.GaussPlan(rows, cols, sigma, 0, rank=r, nranks=P) for r in range(P)]
+        if plans[0].info["algo"] != 1 or (mode_name == "staged" and not plans[0].staged_supported(S)):
+            for pl in plans + [p1]:
+                pl.close()
+            continue
+        ran += 1
+        bf = plans[0].info["block_floats"]
+        recv = [torch.zeros(P * bf, dtype=torch.float32, device="cuda") for _ in range(P)]
+        ptrs = [t.data_ptr() for t in recv]
+        d_img = torch.from_numpy(img).cuda()
+        stripes = [d_img[pl.info["row0"]:pl.info["row0"] + pl.info["valid_rows"]].contiguous() for pl in plans]
+        for r, pl in enumerate(plans):
+            if pl.info["valid_rows"] <= 0:
+                continue
+            if mode_name == "staged":
+                pl.row_pass_staged(stripes[r], ptrs, S)
+            elif mode_name == "peer":
+                pl.row_pass_peer(stripes[r], ptrs)
+            else:
+                pl.row_pass_push(stripes[r], ptrs, 3)
+        outs = []
+        for r, pl in enumerate(plans):
+            oc = torch.zeros((rows, 2 * pl.info["cpp"], 3), dtype=torch.uint8, device="cuda")
+            if mode_name == "staged":
+                for k in range(S):
+                    for q in plans:
+                        q.stage_wait(k)                  # every rank's outgoing copies of sub-range k
+                    pl.col_pass_stage(recv[r], oc, k, S)
+            else:
+                pl.col_pass(recv[r], oc)
+            outs.append(oc)
+        torch.cuda.synchronize()
+        full = torch.cat(outs, 1)[:, :cols]
+        assert torch.equal(full, single), (rows, cols, sigma, P, S, mode_name)
+        for pl in plans + [p1]:
+            pl.close()
+    assert ran >= 3
+
+
 # ---------------------------------------------------------------- full-size properties
 
 def _sample_exact(oracle, img, sigma, pts):
