@@ -53,9 +53,9 @@ def _load() -> C.CDLL:
         "blur_b200_gauss_row_pass_peer": (i32, [vp, vp, C.POINTER(vp), i32, vp]),
         "blur_b200_gauss_row_pass_push": (i32, [vp, vp, C.POINTER(vp), i32, i32, vp]),
         "blur_b200_gauss_staged_supported": (i32, [vp, i32]),
-        "blur_b200_gauss_row_pass_staged": (i32, [vp, vp, C.POINTER(vp), i32, i32, vp]),
+        "blur_b200_gauss_row_pass_staged": (i32, [vp, vp, C.POINTER(vp), i32, i32, i32, i32, vp]),
         "blur_b200_gauss_stage_wait": (i32, [vp, i32, vp]),
-        "blur_b200_gauss_col_pass_stage": (i32, [vp, vp, vp, i32, i32, vp]),
+        "blur_b200_gauss_col_pass_stage": (i32, [vp, vp, vp, i32, i32, i32, vp]),
         "blur_b200_gauss_rowpass_f32": (i32, [vp, vp, vp, vp]),
         "blur_b200_fastboxblur_device": (i32, [vp, i32, i32, i32, i32, i32, i32, vp, vp]),
         "blur_b200_fastboxblur": (i32, [vp, i32, i32, i32, i32, i32]),

@@ -190,21 +190,23 @@ class GaussPlan:
     def staged_supported(self, nstages: int) -> bool:
         return lib.blur_b200_gauss_staged_supported(self._h, int(nstages)) == _lib.OK
 
-    def row_pass_staged(self, d_in_stripe, q_peer_ptrs, nstages: int, stream: int | None = None):
-        """Row pass as `nstages` launches over column sub-ranges; the copy engines push each finished
-        sub-range to its owners under the next launch."""
+    def row_pass_staged(self, d_in_stripe, q_peer_ptrs, nstages: int, stream: int | None = None, store: bool = False,
+                        row_ctas_per_sm: int = 0):
+        """Row pass as `nstages` launches over column sub-ranges.  store=False: the copy engines push each finished
+        sub-range to its owners under the next launch; store=True: every launch writes its sub-ranges straight into
+        the owners' buffers (bulk copies over NVLink), optionally held to `row_ctas_per_sm` CTAs per SM."""
         arr = (C.c_void_p * len(q_peer_ptrs))(*[int(p) for p in q_peer_ptrs])
-        check(lib.blur_b200_gauss_row_pass_staged(self._h, _ptr(d_in_stripe), arr, len(q_peer_ptrs), int(nstages),
-                                                  _stream() if stream is None else stream))
+        check(lib.blur_b200_gauss_row_pass_staged(self._h, _ptr(d_in_stripe), arr, len(q_peer_ptrs), int(nstages), int(bool(store)),
+                                                  int(row_ctas_per_sm), _stream() if stream is None else stream))
 
     def stage_wait(self, stage: int, stream: int | None = None):
         """`stream` waits for this rank's outgoing copies of `stage`."""
         check(lib.blur_b200_gauss_stage_wait(self._h, int(stage), _stream() if stream is None else stream))
 
-    def col_pass_stage(self, d_q_recv, d_out_cols, stage: int, nstages: int, stream: int | None = None):
+    def col_pass_stage(self, d_q_recv, d_out_cols, stage: int, nstages: int, stream: int | None = None, col_ctas_per_sm: int = 0):
         """Column pass + interleave of sub-range `stage` of this rank's column stripe."""
         check(lib.blur_b200_gauss_col_pass_stage(self._h, _ptr(d_q_recv), _ptr(d_out_cols), int(stage), int(nstages),
-                                                 _stream() if stream is None else stream))
+                                                 int(col_ctas_per_sm), _stream() if stream is None else stream))
 
 
 # ---- FastBoxBlur --------------------------------------------------------------------------------

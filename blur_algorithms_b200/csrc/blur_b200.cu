@@ -594,6 +594,7 @@ struct blur_b200_plan {
     static constexpr int kMaxStages = 8;
     cudaEvent_t ev_stage[kMaxStages] = {};
     cudaEvent_t ev_scopy[kMaxStages][7] = {};
+    bool staged_store = false;                     // last staged row pass stored to the peers itself (no copy-engine events)
 };
 
 namespace {
@@ -1315,7 +1316,7 @@ void stage_blocks(const blur_b200_plan* p, int nstages, int k, unsigned char* se
 int blur_b200_gauss_staged_supported(const blur_b200_plan* p, int nstages) { return staged_check(p, nstages); }
 
 int blur_b200_gauss_row_pass_staged(blur_b200_plan* p, const uint8_t* d_in_stripe, float* const* q_peers, int npeers,
-                                    int nstages, void* stream)
+                                    int nstages, int store, int row_ctas_per_sm, void* stream)
 {
     if (!p || !d_in_stripe || !q_peers || npeers != p->nranks || npeers > OlsRowIO::kMaxPeers) return BLUR_B200_EINVAL;
     int rc = staged_check(p, nstages);
@@ -1339,6 +1340,11 @@ int blur_b200_gauss_row_pass_staged(blur_b200_plan* p, const uint8_t* d_in_strip
     const int w = p->cpart / S;
     const size_t blk = static_cast<size_t>(p->stripe_rows) * w;            // floats per (stage, channel, source) block
     const size_t plane = static_cast<size_t>(3) * N * blk;                 // floats per stage
+    p->staged_store = store != 0;
+    // store mode: the launch may be held to fewer CTAs per SM so that the column pass of the previous sub-range
+    // (another stream) finds room beside it while this launch waits on NVLink
+    int row_sms = p->num_sms;
+    if (row_ctas_per_sm > 0) row_sms = std::max(1, p->num_sms * std::min(row_ctas_per_sm, ols2_row_ctas_per_sm()) / ols2_row_ctas_per_sm());
     for (int k = 0; k < S; ++k) {
         OlsRowIO io{};
         io.in = d_in_stripe; io.q = p->d_q;
@@ -1349,18 +1355,20 @@ int blur_b200_gauss_row_pass_staged(blur_b200_plan* p, const uint8_t* d_in_strip
         io.peer = 1; io.rank = rank;
         // virtual part v = (destination d, sub-range kk): own part straight into the own receive buffer, the others
         // into the send buffer at the source-block slot of the destination (the kernel adds rank * blk)
+        // (store mode: every part straight into its owner's receive buffer through bulk copies over NVLink)
         for (int d = 0; d < N; ++d)
             for (int kk = 0; kk < S; ++kk)
-                io.qpeer[d * S + kk] = d == rank ? q_peers[rank] + kk * plane
-                                                 : p->d_q + kk * plane + (static_cast<ptrdiff_t>(d) - rank) * static_cast<ptrdiff_t>(blk);
+                io.qpeer[d * S + kk] = (d == rank || store) ? q_peers[d] + kk * plane
+                                                            : p->d_q + kk * plane + (static_cast<ptrdiff_t>(d) - rank) * static_cast<ptrdiff_t>(blk);
         stage_blocks(p, S, k, io.bsel, io.nbsel);
         io.nunits = io.nbsel * io.npairs;
         if (io.nbsel > 0) {
-            CU_TRY(launch_row_fft(p, io, p->num_sms, st));
+            CU_TRY(launch_row_fft(p, io, row_sms, st));
             ++g_launches;
         }
         if (N == 1) continue;
         CU_TRY(cudaEventRecord(p->ev_stage[k], st));
+        if (store) continue;
         const size_t width = static_cast<size_t>(p->valid_rows) * w * sizeof(float);
         const size_t pitch = static_cast<size_t>(N) * blk * sizeof(float);
         for (int di = 0; di + 1 < N; ++di) {                    // start with the next rank: spread the NVSwitch ports
@@ -1380,11 +1388,16 @@ int blur_b200_gauss_stage_wait(blur_b200_plan* p, int stage, void* stream)
     if (!p || stage < 0 || stage >= blur_b200_plan::kMaxStages) return BLUR_B200_EINVAL;
     if (p->valid_rows <= 0 || p->nranks == 1 || !p->ev_stage[0]) return BLUR_B200_OK;
     CU_TRY(cudaSetDevice(p->device));
+    if (p->staged_store) {
+        CU_TRY(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), p->ev_stage[stage], 0));
+        return BLUR_B200_OK;
+    }
     for (int di = 0; di + 1 < p->nranks; ++di) CU_TRY(cudaStreamWaitEvent(static_cast<cudaStream_t>(stream), p->ev_scopy[stage][di], 0));
     return BLUR_B200_OK;
 }
 
-int blur_b200_gauss_col_pass_stage(blur_b200_plan* p, const float* d_q_recv, uint8_t* d_out_cols, int stage, int nstages, void* stream)
+int blur_b200_gauss_col_pass_stage(blur_b200_plan* p, const float* d_q_recv, uint8_t* d_out_cols, int stage, int nstages,
+                                   int col_ctas_per_sm, void* stream)
 {
     if (!p || !d_q_recv || !d_out_cols || stage < 0 || stage >= nstages) return BLUR_B200_EINVAL;
     int rc = staged_check(p, nstages);
@@ -1406,7 +1419,9 @@ int blur_b200_gauss_col_pass_stage(blur_b200_plan* p, const float* d_q_recv, uin
     io.b0 = 0;
     io.nbl = io.ax.nblocks;
     io.nunits = ols2_col_npairs(io.noct, io.nbl);
-    CU_TRY(launch_ols2_col(io, d_q_recv + stage * plane, w, N * p->stripe_rows, p->d_ols2_tw, p->d_ols2_kt, p->num_sms, st));
+    int col_sms = p->num_sms;
+    if (col_ctas_per_sm > 0) col_sms = std::max(1, p->num_sms * std::min(col_ctas_per_sm, ols2_col_ctas_per_sm()) / ols2_col_ctas_per_sm());
+    CU_TRY(launch_ols2_col(io, d_q_recv + stage * plane, w, N * p->stripe_rows, p->d_ols2_tw, p->d_ols2_kt, col_sms, st));
     ++g_launches;
     const int out_cols = 2 * p->cpp;
     const int valid_cols = std::max(0, std::min(p->cpart, p->cols - p->rank * p->cpart));

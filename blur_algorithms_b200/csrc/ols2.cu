@@ -62,5 +62,7 @@ cudaError_t launch_ols2_col(const OlsColIO& io_in, const float* d_q, int qpitch,
 }
 
 int ols2_row_units_per_sm(int R2) { return R2 == 32 ? BLUR_OLS2_ROW_CTAS * kOls2RowWarps : 0; }
+int ols2_row_ctas_per_sm() { return BLUR_OLS2_ROW_CTAS; }
+int ols2_col_ctas_per_sm() { return BLUR_OLS2_COL_CTAS; }
 
 }  // namespace blurb200

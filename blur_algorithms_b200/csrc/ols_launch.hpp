@@ -19,4 +19,7 @@ cudaError_t launch_ols2_col(const OlsColIO& io, const float* d_q, int qpitch, in
                             const float* kt, int num_sms, cudaStream_t stream);
 // units (= warps) resident per SM in the row pass, for wave-aligned chunking of the sharded plan
 int ols2_row_units_per_sm(int R2);
+// resident CTAs per SM the two-factor kernels are compiled for (callers scale num_sms to hold a launch to fewer)
+int ols2_row_ctas_per_sm();
+int ols2_col_ctas_per_sm();
 }  // namespace blurb200

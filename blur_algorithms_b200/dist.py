@@ -12,6 +12,10 @@ Exchange modes (BLUR_B200_EXCHANGE):
           copies of it have landed (one device-side barrier per sub-range) while the later sub-ranges
           are still on the wire: the exchange hides behind both FFT passes
           (blur_b200_gauss_row_pass_staged / _stage_wait / _col_pass_stage);
+  "sstore" the same sub-range pipeline without copy engines or send buffer: every row launch writes its
+          sub-ranges straight into the owners' buffers with bulk shared->global copies over NVLink and is held to
+          two CTAs per SM; the column pass of sub-range k runs on a second stream in the SMs' remaining
+          room while row launch k+1 waits on the links;
   "push"  the row pass runs in wave-aligned chunks of row pairs; the kernel writes this
           rank's own part into its receive buffer and the rest into a local send buffer, and as soon
           as a chunk is done the GPU's COPY ENGINES move it into the owners' buffers (one 2-D peer
@@ -176,6 +180,10 @@ class ShardedGaussBlur:
         self.exchange_mode = exchange_mode or os.environ.get("BLUR_B200_EXCHANGE", "staged")
         self.nchunks = nchunks or int(os.environ.get("BLUR_B200_CHUNKS", "0")) or {2: 12}.get(self.nranks, 2)
         self.nstages = int(os.environ.get("BLUR_B200_STAGES", "0")) or 4
+        # sstore: CTAs per SM of the row launches / of the column launches that run beside them
+        self.row_ctas = int(os.environ.get("BLUR_B200_SSTORE_ROW_CTAS", "2"))
+        self.col_ctas = int(os.environ.get("BLUR_B200_SSTORE_COL_CTAS", "1"))
+        self._side = None
         self.q_send = None
         want_fused = (fused is not False and row_pass is None and col_pass is None and self.nranks > 1
                       and self.nranks <= 8 and g.algo == 1 and self.device.type == "cuda")
@@ -202,7 +210,7 @@ class ShardedGaussBlur:
             row_pass = self.plan.row_pass
             col_pass = self.plan.col_pass
         self._row_pass, self._col_pass = row_pass, col_pass
-        if self.exchange_mode == "staged":
+        if self.exchange_mode in ("staged", "sstore"):
             # fewer stages if the part does not divide, plain push if the plan cannot run staged at all
             while self.nstages > 1 and not (self.plan is not None and self.symm is not None and self.plan.staged_supported(self.nstages)):
                 self.nstages //= 2
@@ -217,6 +225,11 @@ class ShardedGaussBlur:
         """What moves the float32 intermediate between the ranks (for bench.py's config line)."""
         if not self.fused:
             return "NCCL all_to_all of the float32 intermediate (local send buffer)"
+        if self.exchange_mode == "sstore":
+            return (f"staged store: {self.nstages} column sub-ranges per rank; every row launch writes its sub-ranges straight into "
+                    f"the owners' symmetric-memory buffers (bulk shared->global copies over NVLink, {self.row_ctas} CTAs/SM); the column "
+                    f"pass of a sub-range runs on a second stream ({self.col_ctas} CTA/SM beside the row launches) after a device-side "
+                    "barrier for that sub-range")
         if self.exchange_mode == "staged":
             return (f"staged: {self.nstages} column sub-ranges per rank; row pass sub-range by sub-range, copy engines "
                     "(cudaMemcpy2DAsync peer copies, one per destination and sub-range) push each finished sub-range into the "
@@ -234,8 +247,9 @@ class ShardedGaussBlur:
             return
         if not self.fused:
             self._row_pass(self._last_in, self.q_send)
-        elif self.exchange_mode == "staged":
-            self.plan.row_pass_staged(self._last_in, self.peer_ptrs, self.nstages)
+        elif self.exchange_mode in ("staged", "sstore"):
+            st = self.exchange_mode == "sstore"
+            self.plan.row_pass_staged(self._last_in, self.peer_ptrs, self.nstages, store=st, row_ctas_per_sm=self.row_ctas if st else 0)
             for k in range(self.nstages):
                 self.plan.stage_wait(k)
         elif self.exchange_mode == "store":
@@ -245,7 +259,7 @@ class ShardedGaussBlur:
 
     def col_pass_only(self) -> None:
         """The column phase without barriers (per-pass timing in bench.py)."""
-        if self.fused and self.exchange_mode == "staged":
+        if self.fused and self.exchange_mode in ("staged", "sstore"):
             for k in range(self.nstages):
                 self.plan.col_pass_stage(self.q_recv, self.out_cols, k, self.nstages)
         else:
@@ -263,9 +277,16 @@ class ShardedGaussBlur:
         if self.symm is not None:
             # peers may still be reading their buffers (previous blur's column pass)
             self.symm.barrier(channel=0)
-            if self.exchange_mode == "staged":
+            if self.exchange_mode == "sstore":
+                if self._side is None:
+                    self._side = torch.cuda.Stream(self.device, priority=-1)
+                    self._ev_b0 = torch.cuda.Event()
+                self._ev_b0.record(torch.cuda.current_stream(self.device))       # the second stream starts behind this barrier
+            if self.exchange_mode in ("staged", "sstore"):
                 if self.geom.valid_rows > 0:
-                    self.plan.row_pass_staged(in_stripe, self.peer_ptrs, self.nstages)
+                    st = self.exchange_mode == "sstore"
+                    self.plan.row_pass_staged(in_stripe, self.peer_ptrs, self.nstages, store=st,
+                                              row_ctas_per_sm=self.row_ctas if st else 0)
                 return                                   # the per-stage barriers are in _cols()
             if self.geom.valid_rows > 0:
                 if self.exchange_mode == "store":
@@ -278,8 +299,29 @@ class ShardedGaussBlur:
                 self._row_pass(in_stripe, self.q_send)
             exchange(self.q_send, self.q_recv, self.group, self.geom.algo)
 
-    def _cols(self) -> torch.Tensor:
-        if self.symm is not None and self.exchange_mode == "staged":
+    def _cols(self, after=None) -> torch.Tensor:
+        """`after`: an event the column passes must also wait for (the streamed host path: the previous image's
+        download has left out_cols)."""
+        sstore = self.symm is not None and self.exchange_mode == "sstore"
+        main = torch.cuda.current_stream(self.device) if (sstore or after is not None) else None
+        if after is not None and not sstore:
+            main.wait_event(after)
+        if sstore:
+            # second stream: barrier + column pass of sub-range k as soon as row launch k is done everywhere, beside
+            # the row launches of the later sub-ranges (which mostly wait on NVLink)
+            self._side.wait_event(self._ev_b0)
+            if after is not None:
+                self._side.wait_event(after)
+            with torch.cuda.stream(self._side):
+                for k in range(self.nstages):
+                    if self.geom.valid_rows > 0:
+                        self.plan.stage_wait(k, self._side.cuda_stream)
+                    self.symm.barrier(channel=1 + k)
+                    last = k == self.nstages - 1
+                    self.plan.col_pass_stage(self.q_recv, self.out_cols, k, self.nstages, self._side.cuda_stream,
+                                             col_ctas_per_sm=0 if last else self.col_ctas)
+            main.wait_stream(self._side)
+        elif self.symm is not None and self.exchange_mode == "staged":
             for k in range(self.nstages):
                 if self.geom.valid_rows > 0:
                     self.plan.stage_wait(k)              # this rank's outgoing copies of sub-range k are complete ...
@@ -316,9 +358,7 @@ class ShardedGaussBlur:
             cur.wait_event(ev_up[k])
             self._rows(self._d_in[k])
             ev_row[k].record(cur)
-            if ev_dn is not None:
-                cur.wait_event(ev_dn)                    # image i-1 has left out_cols
-            self._cols()
+            self._cols(after=ev_dn)                      # image i-1 has left out_cols
             ev_c = torch.cuda.Event()
             ev_c.record(cur)
             with torch.cuda.stream(self._s_dn):

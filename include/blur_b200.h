@@ -154,13 +154,18 @@ int blur_b200_gauss_row_pass_push(blur_b200_plan *plan, const uint8_t *d_in_stri
  * blur_b200_gauss_col_pass_stage transforms and interleaves sub-range k of this rank's column stripe — while the
  * later stages are still on the wire.  Receive-buffer layout for this mode: [stage][3][nranks][stripe_rows][w]
  * (same size as the unstaged layout).  blur_b200_gauss_staged_supported: BLUR_B200_OK, or BLUR_B200_ESIZE when the
- * plan / stage count cannot run staged (use blur_b200_gauss_row_pass_push then).  Replaces flip_block, Source.cpp:540. */
+ * plan / stage count cannot run staged (use blur_b200_gauss_row_pass_push then).  Replaces flip_block, Source.cpp:540.
+ * store != 0: no copy engines and no send buffer — launch k's epilogue writes every sub-range straight into its owner's
+ * buffer with bulk shared->global copies over NVLink (the SM-issued path sustains more all-to-all bandwidth than the
+ * copy engines at 8 GPUs); blur_b200_gauss_stage_wait then waits for launch k itself.  row_ctas_per_sm /
+ * col_ctas_per_sm > 0 hold a launch to that many CTAs per SM so that the column pass of sub-range k (issued on a
+ * second stream) runs beside row launch k+1 while that one waits on the links; 0 = the kernels' own occupancy. */
 int blur_b200_gauss_staged_supported(const blur_b200_plan *plan, int nstages);
 int blur_b200_gauss_row_pass_staged(blur_b200_plan *plan, const uint8_t *d_in_stripe, float *const *q_peers, int npeers,
-                                    int nstages, void *stream);
+                                    int nstages, int store, int row_ctas_per_sm, void *stream);
 int blur_b200_gauss_stage_wait(blur_b200_plan *plan, int stage, void *stream);
 int blur_b200_gauss_col_pass_stage(blur_b200_plan *plan, const float *d_q_recv, uint8_t *d_out_cols, int stage, int nstages,
-                                   void *stream);
+                                   int col_ctas_per_sm, void *stream);
 
 /* Parity hook: the float32 row-pass result (`resf` of Source.cpp:536) as planar [3][rows][cols]. */
 int blur_b200_gauss_rowpass_f32(blur_b200_plan *plan, const uint8_t *d_in, float *d_planar, void *stream);

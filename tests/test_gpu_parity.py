@@ -276,7 +276,7 @@ def test_gauss_sharded_emulated_on_one_gpu(bb, torch):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("mode_name", ["staged", "peer", "push"])
+@pytest.mark.parametrize("mode_name", ["staged", "staged_store", "peer", "push"])
 def test_gauss_sharded_exchange_modes_emulated_on_one_gpu(bb, torch, mode_name):
     """The three fused exchange paths (staged sub-ranges, row-kernel peer stores, chunked push) with all P ranks'
     plans in ONE process: the peer pointers are the other plans' receive buffers on the same device.  Results must
@@ -291,7 +291,8 @@ def test_gauss_sharded_exchange_modes_emulated_on_one_gpu(bb, torch, mode_name):
         p1 = bb.GaussPlan(rows, cols, sigma, 0)
         p1.run(single)
         plans = [bb.GaussPlan(rows, cols, sigma, 0, rank=r, nranks=P) for r in range(P)]
-        if plans[0].info["algo"] != 1 or (mode_name == "staged" and not plans[0].staged_supported(S)):
+        staged = mode_name.startswith("staged")
+        if plans[0].info["algo"] != 1 or (staged and not plans[0].staged_supported(S)):
             for pl in plans + [p1]:
                 pl.close()
             continue
@@ -304,8 +305,8 @@ def test_gauss_sharded_exchange_modes_emulated_on_one_gpu(bb, torch, mode_name):
         for r, pl in enumerate(plans):
             if pl.info["valid_rows"] <= 0:
                 continue
-            if mode_name == "staged":
-                pl.row_pass_staged(stripes[r], ptrs, S)
+            if staged:
+                pl.row_pass_staged(stripes[r], ptrs, S, store=mode_name == "staged_store", row_ctas_per_sm=2 if r % 2 else 0)
             elif mode_name == "peer":
                 pl.row_pass_peer(stripes[r], ptrs)
             else:
@@ -313,11 +314,11 @@ def test_gauss_sharded_exchange_modes_emulated_on_one_gpu(bb, torch, mode_name):
         outs = []
         for r, pl in enumerate(plans):
             oc = torch.zeros((rows, 2 * pl.info["cpp"], 3), dtype=torch.uint8, device="cuda")
-            if mode_name == "staged":
+            if staged:
                 for k in range(S):
                     for q in plans:
                         q.stage_wait(k)                  # every rank's outgoing copies of sub-range k
-                    pl.col_pass_stage(recv[r], oc, k, S)
+                    pl.col_pass_stage(recv[r], oc, k, S, col_ctas_per_sm=k % 2)
             else:
                 pl.col_pass(recv[r], oc)
             outs.append(oc)
