@@ -6,13 +6,13 @@ reference's flip_block, Source.cpp:540), column pass on column stripes.  One pro
 On GPUs every rank's receive buffer lives in symmetric memory (torch.distributed._symmetric_memory:
 CUDA peer mappings over NVLink/NVSwitch) and no collective library call is on the data path.
 Exchange modes (BLUR_B200_EXCHANGE):
-  "staged" (default where the plan supports it) every rank's part is cut into column sub-ranges; the row
+  "staged" (default up to 4 GPUs where the plan supports it) every rank's part is cut into column sub-ranges; the row
           pass runs sub-range by sub-range, the copy engines push each finished sub-range to its owners
           under the next one's FFTs, and the column pass of a sub-range starts as soon as every rank's
           copies of it have landed (one device-side barrier per sub-range) while the later sub-ranges
           are still on the wire: the exchange hides behind both FFT passes
           (blur_b200_gauss_row_pass_staged / _stage_wait / _col_pass_stage);
-  "sstore" the same sub-range pipeline without copy engines or send buffer: every row launch writes its
+  "sstore" (measured, not a default) the same sub-range pipeline without copy engines or send buffer: every row launch writes its
           sub-ranges straight into the owners' buffers with bulk shared->global copies over NVLink and is held to
           two CTAs per SM; the column pass of sub-range k runs on a second stream in the SMs' remaining
           room while row launch k+1 waits on the links;
@@ -20,7 +20,7 @@ Exchange modes (BLUR_B200_EXCHANGE):
           rank's own part into its receive buffer and the rest into a local send buffer, and as soon
           as a chunk is done the GPU's COPY ENGINES move it into the owners' buffers (one 2-D peer
           copy per destination) underneath the next chunk's FFTs (blur_b200_gauss_row_pass_push);
-  "store" the row kernel's epilogue stores every result straight into the owner's buffer
+  "store" (default beyond 4 GPUs) the row kernel's epilogue stores every result straight into the owner's buffer
           (blur_b200_gauss_row_pass_peer; bulk shared->global copies from the two-factor kernel): no send
           buffer, but the SMs stay busy until the last byte has crossed NVLink.
 Device-side barriers order the ranks (push / store: two per blur).  Fallback (`fused=False`, or symmetric memory
@@ -177,7 +177,9 @@ class ShardedGaussBlur:
         self.symm = None
         # "push": row pass in chunks + copy kernel over peer mappings (default); "store": the row
         # kernel's epilogue stores remotely itself.  BLUR_B200_EXCHANGE overrides.
-        self.exchange_mode = exchange_mode or os.environ.get("BLUR_B200_EXCHANGE", "staged")
+        # measured defaults (profiles/r02_exchange_modes.txt): up to 4 GPUs the copy-engine sub-range pipeline hides the
+        # exchange behind the FFTs; beyond that the SM-issued bulk stores carry more all-to-all bandwidth
+        self.exchange_mode = exchange_mode or os.environ.get("BLUR_B200_EXCHANGE") or ("staged" if self.nranks <= 4 else "store")
         self.nchunks = nchunks or int(os.environ.get("BLUR_B200_CHUNKS", "0")) or {2: 12}.get(self.nranks, 2)
         self.nstages = int(os.environ.get("BLUR_B200_STAGES", "0")) or 4
         # sstore: CTAs per SM of the row launches / of the column launches that run beside them
