@@ -20,7 +20,7 @@ from ._lib import NYQUIST_EXACT, NYQUIST_PFFFT, BlurB200Error, check, lib
 
 __all__ = [
     "isValidSize", "nearestTransformSize", "gaussian_window", "getGaussian", "gauss_geometry",
-    "pffft_", "pocketfft_1D", "pocketfft_2D", "fastboxblur", "Reflect_101", "deinterleave_BGR",
+    "pffft_", "pocketfft_1D", "pocketfft_2D", "boxfft_blur", "boxfft_klen", "fastboxblur", "Reflect_101", "deinterleave_BGR",
     "interleave_BGR", "flip_block", "dft_image", "Test", "GaussPlan", "fastboxblur_device", "fastboxblur_batch",
     "kernel_launches", "BlurB200Error", "NYQUIST_EXACT", "NYQUIST_PFFFT",
 ]
@@ -99,6 +99,19 @@ def pocketfft_1D(image: np.ndarray, nsmooth: float) -> None:
     check(lib.blur_b200_gauss_u8c3(img.ctypes.data, img.shape[0], img.shape[1], float(nsmooth), NYQUIST_EXACT))
 
 
+def boxfft_klen(rows: int, cols: int, nsmooth: float) -> int:
+    """kLen of the reference's `#define boxblur` build: (int)(ns'^2), ns' = sqrt(min((int)nsmooth^2, min(rows-1, cols-1)))
+    (Source.cpp:287-291)."""
+    return lib.blur_b200_boxfft_klen(int(rows), int(cols), float(nsmooth))
+
+
+def boxfft_blur(image: np.ndarray, nsmooth: float, nyquist_mode: int = NYQUIST_EXACT) -> None:
+    """pocketfft_1D (nyquist_mode EXACT) / pffft_ (PFFFT) of the reference built with `#define boxblur`
+    (Source.cpp:12): FFT convolution with a box of width kLen convolved with itself (box_kernel, :128-140).  In place."""
+    img = _as_image(image)
+    check(lib.blur_b200_boxfft_u8c3(img.ctypes.data, img.shape[0], img.shape[1], float(nsmooth), nyquist_mode))
+
+
 def pocketfft_2D(image: np.ndarray, nsmooth: float) -> None:
     """pocketfft_2D(cv::Mat& image, double nsmooth), Source.cpp:143-277 (blur branch).  In place.
     The 2-D formulation computes the same separable reflect-101 convolution as pocketfft_1D and
@@ -111,11 +124,17 @@ class GaussPlan:
     one (rows, cols, sigma) problem.  Replaces the per-call setup of Source.cpp:465-503."""
 
     def __init__(self, rows: int, cols: int, sigma: float, nyquist_mode: int = NYQUIST_EXACT,
-                 device: int = 0, rank: int = 0, nranks: int = 1):
+                 device: int = 0, rank: int = 0, nranks: int = 1, boxblur: bool = False):
+        """boxblur=True: the reference's `#define boxblur` build — `sigma` is then its nsmooth and the kernel a box
+        of width kLen = boxfft_klen(rows, cols, nsmooth) convolved with itself (Source.cpp:128-140, 287-291)."""
         self._h = C.c_void_p()
         self.rows, self.cols, self.sigma = rows, cols, float(sigma)
         self.rank, self.nranks = rank, nranks
-        if nranks == 1:
+        if boxblur:
+            if nranks != 1:
+                raise BlurB200Error(_lib.EINVAL, "the FFT box blur is a single-GPU plan")
+            check(lib.blur_b200_boxfft_plan_create(C.byref(self._h), rows, cols, float(sigma), nyquist_mode, device))
+        elif nranks == 1:
             check(lib.blur_b200_gauss_plan_create(C.byref(self._h), rows, cols, float(sigma), nyquist_mode, device))
         else:
             check(lib.blur_b200_gauss_plan_create_sharded(C.byref(self._h), rows, cols, float(sigma), nyquist_mode,

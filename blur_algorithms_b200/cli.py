@@ -88,11 +88,22 @@ def resize(img: np.ndarray, rows: int, cols: int) -> np.ndarray:
     return np.ascontiguousarray(img[ri, ci])
 
 
-def run_test(image: np.ndarray, flag: int, nsmooth: float, quiet: bool = False) -> float:
-    """`Test(image, flag, nsmooth)` (Source.cpp:574-608): blurs `image` in place, returns elapsed ms."""
+def run_test(image: np.ndarray, flag: int, nsmooth: float, quiet: bool = False, boxblur: bool = False) -> float:
+    """`Test(image, flag, nsmooth)` (Source.cpp:574-608): blurs `image` in place, returns elapsed ms.
+    boxblur: the reference built with `#define boxblur` (Source.cpp:12) — flags 5 / 3 / 2 convolve with box_kernel's tent
+    through the FFT kernels, flag 1 is cv::blur twice (:597-600)."""
     import blur_algorithms_b200 as bb
     t0 = time.perf_counter()
-    if flag == 5:
+    if boxblur and flag in (5, 3, 2):
+        bb.boxfft_blur(image, nsmooth, bb.NYQUIST_PFFFT if flag == 3 else bb.NYQUIST_EXACT)
+    elif boxblur and flag not in (4,):
+        cv2 = _cv2()
+        if cv2 is None:
+            raise SystemExit("flag 1 is the reference's OpenCV baseline; cv2 is not importable here")
+        k = int(nsmooth) * int(nsmooth)
+        for _ in range(2):
+            cv2.blur(image, (k, k), dst=image, borderType=cv2.BORDER_REFLECT_101)
+    elif flag == 5:
         bb.pocketfft_1D(image, nsmooth)
     elif flag == 4:
         rows, cols = image.shape[:2]
@@ -163,6 +174,7 @@ def main(argv=None) -> int:
     ap.add_argument("file")
     ap.add_argument("-o", "--out")
     ap.add_argument("--sweep", action="store_true")
+    ap.add_argument("--boxblur", action="store_true", help="the reference's `#define boxblur` build: tent kernel through the FFT path")
     ap.add_argument("--compare-cv2", action="store_true",
                     help="also run cv2.GaussianBlur / cv2.blur on the input and report the difference")
     a = ap.parse_args(argv)
@@ -171,7 +183,7 @@ def main(argv=None) -> int:
         sweep(image, a.flag)
         return 0
     src = image.copy() if a.compare_cv2 else None
-    run_test(image, a.flag, a.nsmooth)
+    run_test(image, a.flag, a.nsmooth, boxblur=a.boxblur)
     out = a.out or (os.path.splitext(a.file)[0] + "_blur" + (os.path.splitext(a.file)[1] or ".ppm"))
     if a.file == "synthetic" and not a.out:
         out = "synthetic_blur.ppm"

@@ -677,8 +677,9 @@ int plan_create_impl(blur_b200_plan* p, const GaussGeometry& gg, int rows, int c
 
 int plan_create(blur_b200_plan** out, int rows, int cols, double sigma, int mode, int device, int rank, int nranks)
 {
-    if (!out || rows < 1 || cols < 1 || !(sigma > 0) || (mode != 0 && mode != 1) || nranks < 1 || rank < 0 ||
-        rank >= nranks)
+    // sigma < 0: FFT box blur, sigma = -kLen (fft_plan.hpp, "kernel kinds"); only blur_b200_boxfft_* pass it
+    if (!out || rows < 1 || cols < 1 || !(sigma > 0 || (sigma <= -3 && box_klen(sigma) % 2 == 1)) || (mode != 0 && mode != 1) ||
+        nranks < 1 || rank < 0 || rank >= nranks)
         return BLUR_B200_EINVAL;
     *out = nullptr;
     const GaussGeometry gg = gauss_geometry(rows, cols, sigma);
@@ -1147,6 +1148,47 @@ int blur_b200_gauss_u8c3(uint8_t* h_bgr, int rows, int cols, double sigma, int n
     }
     if (!cached) {
         const int rc = blur_b200_gauss_plan_create(&cached, rows, cols, sigma, nyquist_mode, dev);
+        if (rc) { cached = nullptr; return rc; }
+    }
+    const int rc = blur_b200_gauss_run_host(cached, h_bgr, h_bgr);
+    if (rc) { blur_b200_gauss_plan_destroy(cached); cached = nullptr; }
+    return rc;
+}
+
+// ---- FFT box blur: the reference built with `#define boxblur` (Source.cpp:12) ---------------------
+int blur_b200_boxfft_klen(int rows, int cols, double nsmooth)
+{
+    if (rows < 1 || cols < 1 || !(nsmooth >= 0)) return 0;
+    return boxfft_klen(rows, cols, nsmooth);
+}
+
+int blur_b200_boxfft_plan_create(blur_b200_plan** plan, int rows, int cols, double nsmooth, int nyquist_mode, int device)
+{
+    if (!plan || rows < 1 || cols < 1 || !(nsmooth > 0)) return BLUR_B200_EINVAL;
+    const int klen = boxfft_klen(rows, cols, nsmooth);
+    // even kLen: the reference's pad (kLen - 1) / 2 * 2 is one short of the tent's half width and its outermost
+    // taps wrap around the tile — undefined there, refused here; kLen = 1 is the identity
+    if (klen < 3 || klen % 2 == 0) return BLUR_B200_EINVAL;
+    return plan_create(plan, rows, cols, -static_cast<double>(klen), nyquist_mode, device, 0, 1);
+}
+
+int blur_b200_boxfft_u8c3(uint8_t* h_bgr, int rows, int cols, double nsmooth, int nyquist_mode)
+{
+    if (!h_bgr || rows < 1 || cols < 1 || !(nsmooth > 0)) return BLUR_B200_EINVAL;
+    const int klen = boxfft_klen(rows, cols, nsmooth);
+    if (klen < 3 || klen % 2 == 0) return BLUR_B200_EINVAL;
+    blur_b200_plan*& cached = g_oneshot_plan;
+    std::lock_guard<std::mutex> lock(g_oneshot_mu);
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess) { g_cuda_err = "cudaGetDevice failed (no CUDA device?)"; return BLUR_B200_ECUDA; }
+    const double key = -static_cast<double>(klen);
+    if (cached && (cached->rows != rows || cached->cols != cols || cached->sigma != key || cached->mode != nyquist_mode ||
+                   cached->device != dev)) {
+        blur_b200_gauss_plan_destroy(cached);
+        cached = nullptr;
+    }
+    if (!cached) {
+        const int rc = plan_create(&cached, rows, cols, key, nyquist_mode, dev, 0, 1);
         if (rc) { cached = nullptr; return rc; }
     }
     const int rc = blur_b200_gauss_run_host(cached, h_bgr, h_bgr);

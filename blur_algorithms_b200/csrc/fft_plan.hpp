@@ -45,10 +45,47 @@ inline int nearest_transform_size(int n)
     return n;
 }
 
+// ---- kernel kinds ----------------------------------------------------------------------------
+// Throughout the planning code a NEGATIVE `sigma` selects the FFT box blur of the reference's
+// `#define boxblur` build (Source.cpp:12; box_kernel :128-140; branches :287-291,437-441,468-495):
+// sigma = -kLen, taps = a box of width kLen convolved with itself (tent of 2 kLen - 1 taps), pad = kLen - 1.
+// It flows through get_gaussian / gauss_geometry / kernel_spectrum like a Gaussian's (sigma, width) pair.
+inline bool is_box_sigma(double sigma) { return sigma < 0; }
+inline int box_klen(double sigma) { return static_cast<int>(-sigma + 0.5); }
+
+// Source.cpp:287-291 = :437-441: the boxblur build replaces nsmooth by sqrt(min((int)ns^2, min(rows-1, cols-1)))
+// and takes kSize = kLen = (int)(nsmooth'^2) (double arithmetic, truncation).
+inline int boxfft_klen(int rows, int cols, double nsmooth)
+{
+    const int m = std::min(static_cast<int>(nsmooth) * static_cast<int>(nsmooth), std::min(rows - 1, cols - 1));
+    if (m < 0) return 0;
+    const double ns = std::sqrt(static_cast<double>(m));
+    return static_cast<int>(ns * ns);
+}
+
+// Source.cpp:128-140, float storage accumulated exactly like the reference (`kernel[i] += double`
+// rounds on every addition); the icol loop runs to kLen + 1 as there (those terms clamp to 0).
+inline void box_kernel_1d(std::vector<float>& kernel, int kLen, int fft_length)
+{
+    kernel.assign(static_cast<size_t>(fft_length), 0.f);
+    const double scale = 1.0 / std::pow(static_cast<double>(kLen), 4);
+    for (int irow = -kLen + 1; irow <= kLen - 1; ++irow)
+        for (int icol = -kLen + 1; icol <= kLen + 1; ++icol) {
+            const double kval = static_cast<double>((kLen - std::abs(irow)) * (kLen - std::abs(icol)));
+            const double v = std::min(std::max(kval * scale, 0.0), 1.0);
+            float& k = kernel[static_cast<size_t>((icol + fft_length) % fft_length)];
+            k = static_cast<float>(k + v);
+        }
+}
+
 // Reference: Source.cpp:75-102.  float loop variable, float y*y, double exp/normalise, float
 // storage, then rotate left by width/2 so the centre tap is element 0.
 inline void get_gaussian(std::vector<float>& kernel, double sigma, int width = 0, int fft_length = 0)
 {
+    if (is_box_sigma(sigma)) {          // tent taps of the boxblur build, centre at element 0 (fft_length > 2 kLen + 1)
+        box_kernel_1d(kernel, box_klen(sigma), fft_length ? fft_length : 2 * box_klen(sigma) + 3);
+        return;
+    }
     if (!width) width = gaussian_window(sigma);
     kernel.assign(static_cast<size_t>(fft_length ? fft_length : width), 0.f);
     const float mid_w = (width - 1) / 2.f;
@@ -74,8 +111,8 @@ inline GaussGeometry gauss_geometry(int rows, int cols, double sigma)
 {
     GaussGeometry g{};
     g.rows = rows; g.cols = cols;
-    g.ksize = gaussian_window(sigma, std::max(rows, cols));
-    g.pad = (g.ksize - 1) / 2;
+    g.ksize = is_box_sigma(sigma) ? 2 * box_klen(sigma) - 1 : gaussian_window(sigma, std::max(rows, cols));
+    g.pad = (g.ksize - 1) / 2;          // box: kLen - 1 = (kSize - 1) / 2 * passes of Source.cpp:292 for odd kLen
     g.n_col = rows + 2 * g.pad;
     g.n_row = cols + 2 * g.pad;
     if (!is_valid_size(g.n_col)) g.n_col = nearest_transform_size(g.n_col);

@@ -95,6 +95,11 @@ inline void pocketfft_2D_DFT_image(uint8_t* image_data, int rows, int cols, doub
     blur_b200::check(blur_b200_dft_image_host(image_data, image_data, rows, cols, nsmooth, nullptr, padded), "DFT_image");
 }
 
+// The same three entry points of the reference built with `#define boxblur` (Source.cpp:12): FFT convolution with
+// box_kernel's tent (Source.cpp:128-140) instead of the Gaussian.  pffft = true reproduces pffft_'s Nyquist quirk.
+inline void boxblur_fft(uint8_t* image_data, int rows, int cols, double nsmooth, bool pffft = false)
+{ blur_b200::check(blur_b200_boxfft_u8c3(image_data, rows, cols, nsmooth, pffft ? BLUR_B200_NYQUIST_PFFFT : BLUR_B200_NYQUIST_EXACT), "boxblur_fft"); }
+
 // FastBoxBlur's entry as called at Source.cpp:587: in place.
 inline void fastboxblur(uint8_t* in, int w, int h, int channels, int ksize, int passes)
 { blur_b200::check(blur_b200_fastboxblur(in, w, h, channels, ksize, passes), "fastboxblur"); }

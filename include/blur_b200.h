@@ -170,6 +170,16 @@ int blur_b200_gauss_col_pass_stage(blur_b200_plan *plan, const float *d_q_recv, 
 /* Parity hook: the float32 row-pass result (`resf` of Source.cpp:536) as planar [3][rows][cols]. */
 int blur_b200_gauss_rowpass_f32(blur_b200_plan *plan, const uint8_t *d_in, float *d_planar, void *stream);
 
+/* ---- FFT box blur: the reference built with `#define boxblur` (Source.cpp:12) ------------------
+ * pffft_ / pocketfft_1D / pocketfft_2D then convolve with a box of width kLen convolved with itself
+ * (box_kernel, Source.cpp:128-140: a tent of 2*kLen-1 taps) instead of the Gaussian; kLen =
+ * (int)(ns'*ns'), ns' = sqrt(min((int)nsmooth^2, min(rows-1, cols-1))) (:287-291, :437-441), pad = kLen-1.
+ * The plan is an ordinary blur_b200_plan: every blur_b200_gauss_run_* entry applies.  Odd kLen >= 3
+ * only (an even kLen wraps its outermost taps around the tile in the reference): BLUR_B200_EINVAL. */
+int blur_b200_boxfft_klen(int rows, int cols, double nsmooth);
+int blur_b200_boxfft_plan_create(blur_b200_plan **plan, int rows, int cols, double nsmooth, int nyquist_mode, int device);
+int blur_b200_boxfft_u8c3(uint8_t *h_bgr, int rows, int cols, double nsmooth, int nyquist_mode);
+
 /* ---- FastBoxBlur (fastboxblur(in,w,h,channels,ksize,passes), call site Source.cpp:587) ------
  * Declared semantics (upstream source absent): r=(ksize-1)/2, k=2r+1,
  * reflect-101, horizontal then vertical sliding sums, uint8 after each 1-D pass with

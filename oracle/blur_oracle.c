@@ -94,11 +94,57 @@ int orc_nearest_transform_size(int N)
     return N;
 }
 
+/* The reference's compile-time macro `boxblur` (Source.cpp:12) as a run-time switch: when on, the
+ * pipelines below take the `#ifdef boxblur` branches (Source.cpp:152-156,207-211,224-228,287-291,
+ * 325-329,338-342,437-441,468-472,491-495): a tent kernel (box convolved with itself) instead of
+ * the Gaussian.  Not thread safe; the tests set it around single calls. */
+static int g_boxblur = 0;
+void orc_set_boxblur(int on) { g_boxblur = on ? 1 : 0; }
+
+/* Source.cpp:128-140: 1-D box kernel convolved by itself, accumulated in float storage exactly like the
+ * reference (`kernel[i] += double` rounds to float on every addition); the icol loop runs to kLen + 1
+ * like the reference's (those terms clamp to 0).  kernel must be zeroed, fft_length floats. */
+void orc_box_kernel_1d(float *kernel, int kLen, int fft_length)
+{
+    const double scale = 1. / pow((double)kLen, 4);
+    for (int irow = -kLen + 1; irow <= kLen - 1; irow++)
+        for (int icol = -kLen + 1; icol <= kLen + 1; icol++) {
+            const double kval = (double)((kLen - abs(irow)) * (kLen - abs(icol)));
+            double v = kval * scale;
+            v = v < 0. ? 0. : (v > 1. ? 1. : v);
+            float *k = &kernel[(icol + fft_length) % fft_length];
+            *k = (float)(*k + v);
+        }
+}
+
+/* nsmooth / kSize / pad of either build: Source.cpp:283-292 = :432-442 = :148-157 */
+static void kernel_geometry(int rows, int cols, double *nsmooth, int *kSize, int *pad)
+{
+    *kSize = orc_gaussian_window(*nsmooth, rows > cols ? rows : cols);
+    int passes = 1;
+    if (g_boxblur) {
+        int m = (int)*nsmooth * (int)*nsmooth;
+        const int lim = (rows < cols ? rows : cols) - 1;
+        if (lim < m) m = lim;
+        *nsmooth = sqrt((double)m);
+        passes = 2;
+        *kSize = (int)(*nsmooth * *nsmooth);
+    }
+    *pad = (*kSize - 1) / 2 * passes;
+}
+
+/* taps of either build, centred at index 0 of an fft_length array (zeroed by the caller) */
+static void kernel_taps(float *taps, double nsmooth, int kSize, int fft_length)
+{
+    if (g_boxblur) orc_box_kernel_1d(taps, (int)(nsmooth * nsmooth), fft_length);
+    else orc_get_gaussian(taps, nsmooth, kSize, fft_length);
+}
+
 /* Source.cpp:434-457 (identical in pocketfft_1D :284-306) */
 void orc_gauss_sizes(int rows, int cols, double sigma, int out[6])
 {
-    const int kSize = orc_gaussian_window(sigma, rows > cols ? rows : cols);
-    const int pad = (kSize - 1) / 2;
+    int kSize, pad;
+    kernel_geometry(rows, cols, &sigma, &kSize, &pad);
     int sizes[2] = { rows + pad * 2, cols + pad * 2 };
     int tz[2] = { 0, 0 };
     for (int i = 0; i < 2; ++i) {
@@ -206,7 +252,7 @@ static int axis_plan_init(axis_plan *ap, int n, double sigma, int kSize)
     ocpx *spec = (ocpx *)malloc(sizeof(ocpx) * (size_t)(n / 2 + 1));
     ocpx *scr = (ocpx *)malloc(sizeof(ocpx) * (size_t)(n / 2));
     if (!ap->half || !ap->kre || !taps || !spec || !scr) return 1;
-    orc_get_gaussian(taps, sigma, kSize, n);
+    kernel_taps(taps, sigma, kSize, n);
     offt_r2c(ap->half, taps, spec, scr);
     for (int k = 0; k <= n / 2; ++k) ap->kre[k] = spec[k].re;
     free(taps); free(spec); free(scr);
@@ -276,6 +322,10 @@ int orc_gauss_blur_1d_f32(const uint8_t *bgr, int rows, int cols, double sigma, 
     int sz[6];
     orc_gauss_sizes(rows, cols, sigma, sz);
     const int kSize = sz[0], pad = sz[1];
+    {   /* boxblur build: nsmooth itself is replaced (Source.cpp:288,438) before the taps are made */
+        int ks, pd;
+        kernel_geometry(rows, cols, &sigma, &ks, &pd);
+    }
     if (pad > rows - 1 || pad > cols - 1 || pad < 0) return 2;   /* README.md:33-38 */
     const size_t nd = (size_t)rows * cols;
     float *planes = (float *)malloc(sizeof(float) * nd * 3);
@@ -321,12 +371,13 @@ typedef struct {
     int border[4];      /* top bottom left right, Source.cpp:160-176 */
     int sizes[2];
     int kSize, pad;
+    double nsmooth;        /* after the boxblur adjustment (:153) */
 } geom2d;
 
 static void geom2d_init(geom2d *g, int rows, int cols, double sigma)
 {
-    g->kSize = orc_gaussian_window(sigma, rows > cols ? rows : cols);   /* :149 */
-    g->pad = (g->kSize - 1) / 2;                                        /* :157 */
+    kernel_geometry(rows, cols, &sigma, &g->kSize, &g->pad);            /* :149-157 */
+    g->nsmooth = sigma;
     for (int i = 0; i < 4; ++i) g->border[i] = g->pad;
     g->sizes[0] = rows + 2 * g->pad;
     g->sizes[1] = cols + 2 * g->pad;
@@ -429,12 +480,12 @@ static int run_2d(const uint8_t *bgr, uint8_t *out_u8, int rows, int cols, doubl
         float *taps = (float *)calloc((size_t)(H > W ? H : W), sizeof(float));
         ocpx *spec = (ocpx *)malloc(sizeof(ocpx) * (size_t)((H > W ? H : W) / 2 + 1));
         ocpx *scr = (ocpx *)malloc(sizeof(ocpx) * (size_t)((H > W ? H : W) / 2));
-        orc_get_gaussian(taps, sigma, g.kSize, H);
+        kernel_taps(taps, g.nsmooth, g.kSize, H);
         offt_r2c(half_h, taps, spec, scr);
         for (int k = 0; k <= H / 2; ++k) kcol[k] = spec[k].re;
         for (int k = H / 2 + 1; k < H; ++k) kcol[k] = kcol[H - k];
         memset(taps, 0, sizeof(float) * (size_t)(H > W ? H : W));
-        orc_get_gaussian(taps, sigma, g.kSize, W);
+        kernel_taps(taps, g.nsmooth, g.kSize, W);
         offt_r2c(half_w, taps, spec, scr);
         for (int k = 0; k < WC; ++k) krow[k] = spec[k].re;
         free(taps); free(spec); free(scr);

@@ -46,6 +46,12 @@ void orc_flip_block_f32(const float *in, float *out, int w, int h);
  * length) out[3]=sizes[1] (row FFT length) out[4..5]=trailing zeros per axis */
 void orc_gauss_sizes(int rows, int cols, double sigma, int out[6]);
 
+/* `#define boxblur` build of the reference (Source.cpp:12) as a run-time switch: the Gaussian pipelines
+ * below take the reference's boxblur branches (tent kernel = box convolved with itself, kLen =
+ * (int)(nsmooth'^2), pad = (kLen-1)/2*2).  orc_box_kernel_1d: Source.cpp:128-140. */
+void orc_set_boxblur(int on);
+void orc_box_kernel_1d(float *kernel, int kLen, int fft_length);
+
 /* nyquist_mode: 0 = exact multiply on all bins (pocketfft_1D, Source.cpp:280-392),
  *               1 = pffft ordered-layout quirk (pffft_, Source.cpp:414-427, 429-570).
  * In place on interleaved 3-channel uint8.  If rowpass_out != NULL it receives the

@@ -65,6 +65,8 @@ class Oracle:
         L.orc_fastboxblur.restype = C.c_int
         L.orc_num_threads.restype = C.c_int
         L.orc_set_num_threads.argtypes = [C.c_int]
+        L.orc_set_boxblur.argtypes = [C.c_int]
+        L.orc_box_kernel_1d.argtypes = [_f32p, C.c_int, C.c_int]
 
     # --- sizing / taps
     def gaussian_window(self, sigma: float, max_width: int = 0) -> int:
@@ -138,6 +140,20 @@ class Oracle:
             raise ValueError(f"oracle gauss_blur_1d rc={rc}")
         return out
 
+    def boxfft_blur(self, img: np.ndarray, nsmooth: float, nyquist_mode: int = 0) -> np.ndarray:
+        """The reference's `#define boxblur` build of pocketfft_1D / pffft_ (tent kernel, Source.cpp:287-291,
+        437-441, box_kernel :128-140)."""
+        self.lib.orc_set_boxblur(1)
+        try:
+            return self.gauss_blur_1d(img, nsmooth, nyquist_mode)
+        finally:
+            self.lib.orc_set_boxblur(0)
+
+    def box_kernel_1d(self, klen: int, fft_length: int) -> np.ndarray:
+        out = np.zeros(fft_length, np.float32)
+        self.lib.orc_box_kernel_1d(out, klen, fft_length)
+        return out
+
     def gauss_blur_2d(self, img: np.ndarray, sigma: float) -> np.ndarray:
         out = np.ascontiguousarray(img, np.uint8).copy()
         rows, cols = out.shape[:2]
@@ -189,8 +205,8 @@ class Reference:
     """oracle/_ref/libblurref(.so|_dft.so): the reference's Source.cpp + Utils.hpp compiled
     unmodified against API shims.  Raises FileNotFoundError if it has not been built."""
 
-    def __init__(self, dft_image: bool = False) -> None:
-        name = "libblurref_dft.so" if dft_image else "libblurref.so"
+    def __init__(self, dft_image: bool = False, boxblur: bool = False) -> None:
+        name = "libblurref_box.so" if boxblur else ("libblurref_dft.so" if dft_image else "libblurref.so")
         path = os.path.join(ORACLE_DIR, "_ref", name)
         if not os.path.exists(path):
             raise FileNotFoundError(path)
@@ -211,8 +227,8 @@ class Reference:
         L.ref_set_num_threads.argtypes = [C.c_int]
 
     @staticmethod
-    def available(dft_image: bool = False) -> bool:
-        name = "libblurref_dft.so" if dft_image else "libblurref.so"
+    def available(dft_image: bool = False, boxblur: bool = False) -> bool:
+        name = "libblurref_box.so" if boxblur else ("libblurref_dft.so" if dft_image else "libblurref.so")
         return os.path.exists(os.path.join(ORACLE_DIR, "_ref", name))
 
     def gaussian_window(self, sigma: float, max_width: int = 0) -> int:

@@ -576,6 +576,33 @@ def test_layout_templates_other_types(bb, torch):
     assert torch.equal(t, img.permute(1, 0, 2).contiguous())
 
 
+# ---------------------------------------------------------------- FFT box blur (`#define boxblur`)
+
+@pytest.mark.gpu
+def test_boxfft_vs_oracle(bb, oracle, torch):
+    """The reference built with `#define boxblur` (Source.cpp:12): pocketfft_1D / pffft_ with box_kernel's tent
+    (:128-140) instead of the Gaussian, through the same kernels; +-1 LSB against the oracle's boxblur branches
+    (which equal the reference's own boxblur build bit for bit, tests/test_oracle.py)."""
+    for rows, cols, ns in [(120, 160, 3.0), (300, 200, 5.0), (50, 400, 9.0), (1080, 1920, 5.0), (700, 1000, 15.0)]:
+        img = synth("noise", rows, cols, 3)
+        for mode in (0, 1):
+            out = img.copy()
+            bb.boxfft_blur(out, ns, mode)
+            ref = oracle.boxfft_blur(img, ns, mode)
+            assert lsb(out, ref) <= 1, (rows, cols, ns, mode)
+    # plan form, device resident
+    rows, cols, ns = 1080, 1920, 5.0
+    plan = bb.GaussPlan(rows, cols, ns, 0, boxblur=True)
+    assert plan.info["kSize"] == 2 * bb.boxfft_klen(rows, cols, ns) - 1 and plan.info["pad"] == bb.boxfft_klen(rows, cols, ns) - 1
+    img = synth("noise", rows, cols, 4)
+    d = torch.from_numpy(img).cuda()
+    plan.run(d)
+    assert lsb(d.cpu().numpy(), oracle.boxfft_blur(img, ns, 0)) <= 1
+    plan.close()
+    with pytest.raises(bb.BlurB200Error):
+        bb.boxfft_blur(img.copy(), 4.0)                 # even kLen: refused
+
+
 # ---------------------------------------------------------------- DFT_image
 
 def test_dft_image_vs_oracle_and_golden(bb, oracle):

@@ -95,6 +95,24 @@ def test_every_valid_fft_length_plans_and_transforms(emu, oracle):
         assert max(np.abs(outr - a).max(), np.abs(outi - b).max()) < 3e-5, N
 
 
+def test_boxfft_device_code_on_cpu_matches_oracle(emu, oracle):
+    """FFT box blur (the reference's `#define boxblur` build, Source.cpp:12,128-140): the device code runs the tent
+    taps through the same overlap-save kernels (kernel kind = negative sigma, csrc/fft_plan.hpp)."""
+    import blur_algorithms_b200 as bb
+    for rows, cols, ns in [(120, 160, 3.0), (300, 200, 5.0), (200, 333, 7.0), (50, 400, 9.0)]:
+        img = synth("noise", rows, cols, 3)
+        klen = bb.boxfft_klen(rows, cols, ns)
+        m = min(int(ns) * int(ns), min(rows - 1, cols - 1))
+        assert klen == int(np.sqrt(m) * np.sqrt(m)) and klen % 2 == 1
+        for mode in (0, 1):
+            ref = oracle.boxfft_blur(img, ns, mode)
+            out = emu.gauss(img, -float(klen), mode, 1)[0]
+            assert np.abs(out.astype(int) - ref.astype(int)).max() <= 1, (rows, cols, ns, mode)
+    assert bb.boxfft_klen(100, 100, 4.0) == 16            # even: the plan entry refuses it
+    with pytest.raises(bb.BlurB200Error):
+        bb.GaussPlan(100, 100, 4.0, boxblur=True)
+
+
 @pytest.mark.parametrize("rows,cols,sigma", [(64, 96, 2.0), (100, 75, 3.0), (135, 241, 6.0), (240, 320, 5.0), (467, 700, 7.5)])
 def test_device_code_on_cpu_matches_oracle(emu, oracle, rows, cols, sigma):
     img = synth("noise", rows, cols, 5)

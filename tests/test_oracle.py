@@ -214,6 +214,40 @@ def test_oracle_equals_reference_at_1080p_and_4k(oracle):
             assert np.array_equal(lattice(out), gold[key + "_lattice"]), key
 
 
+def test_boxblur_build_tent_kernel_and_reference(oracle):
+    """`#define boxblur` (Source.cpp:12): box_kernel's 1-D taps are the tent (kLen - |i|) / kLen^2 (:128-140), the
+    pipeline is a reflect-101 tent convolution per axis, and the restatement equals the reference's own boxblur
+    build (oracle/_ref/libblurref_box.so) bit for bit."""
+    k = 9
+    taps = oracle.box_kernel_1d(k, 64)
+    want = np.zeros(64)
+    for i in range(-k + 1, k):
+        want[i % 64] = (k - abs(i)) / k ** 2
+    assert np.abs(taps - want).max() < 1e-7 and abs(float(taps.sum()) - 1.0) < 1e-6
+    img = synth("noise", 120, 160, 3)
+    t = np.array([(k - abs(i)) / k ** 2 for i in range(-k + 1, k)])
+
+    def conv(a, axis):
+        ap = np.pad(a.astype(np.float64), [(k - 1, k - 1) if ax == axis else (0, 0) for ax in range(3)], mode="reflect")
+        out = np.zeros(a.shape)
+        for j, w in enumerate(t):
+            sl = [slice(None)] * 3
+            sl[axis] = slice(j, j + a.shape[axis])
+            out += w * ap[tuple(sl)]
+        return out
+    exact = np.floor(conv(conv(img, 1), 0) + 0.5).astype(int)
+    got = oracle.boxfft_blur(img, 3.0, 0)
+    assert np.abs(got.astype(int) - exact).max() <= 1 and (got.astype(int) != exact).mean() < 1e-3
+    from oracle_lib import Reference
+    if not Reference.available(boxblur=True):
+        pytest.skip("oracle/_ref/libblurref_box.so not built (needs /root/reference)")
+    ref = Reference(boxblur=True)
+    for rows, cols, ns in [(120, 160, 3.0), (300, 200, 5.0), (50, 400, 9.0)]:
+        im = synth("noise", rows, cols, 3)
+        for flag, mode in ((5, 0), (3, 1)):
+            assert np.array_equal(ref.test(im, flag, ns), oracle.boxfft_blur(im, ns, mode)), (rows, cols, ns, flag)
+
+
 def test_pffft_quirk_is_rank_one_correction(oracle):
     """The identity DESIGN.md 3.1a builds on: the oracle's pffft-mode row pass (Source.cpp:414-427)
     equals the exact row pass + c (-1)^x A per line, A = weighted alternating sum of the line
