@@ -567,6 +567,8 @@ struct blur_b200_plan {
     int qpitch = 0, cpart = 0;        // overlap-save Q: floats per row / image columns per part
     float* d_q = nullptr;             // [nranks] blocks
     uint8_t* d_u = nullptr;           // [3][2*cpp][rows]
+    int* d_cnt = nullptr;             // fused interleave of the two-factor column kernel: arrival counters per item
+    bool col_fuse = false;            // BLUR_B200_COL_FUSE=1 at plan creation
     // pffft Nyquist quirk served by the overlap-save kernels (single GPU): per-line corrections
     bool quirk_ols = false;
     double quirk_c_row = 0, quirk_c_col = 0;      // (K[0] - K[N/2]) / N of each axis
@@ -745,6 +747,12 @@ int plan_create_impl(blur_b200_plan* p, const GaussGeometry& gg, int rows, int c
     CU_TRY(cudaMalloc(&p->d_q, sizeof(float) * p->block_floats * nranks));
     CU_TRY(cudaMemset(p->d_q, 0, sizeof(float) * p->block_floats * nranks));   // phantom column of an odd width stays 0
     CU_TRY(cudaMalloc(&p->d_u, static_cast<size_t>(3) * 2 * p->cpp * rows));
+    if (const char* e = std::getenv("BLUR_B200_COL_FUSE")) p->col_fuse = std::atoi(e) != 0;
+    if (p->col_fuse && p->algo == 1 && p->ols_col.R2) {
+        const size_t n = static_cast<size_t>(p->qpitch / 32 + 2) * p->ols_col.nblocks;
+        CU_TRY(cudaMalloc(&p->d_cnt, sizeof(int) * n));
+        CU_TRY(cudaMemset(p->d_cnt, 0, sizeof(int) * n));
+    }
     CU_TRY(cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking));
     return BLUR_B200_OK;
 }
@@ -824,8 +832,19 @@ int run_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, float* d_q, cuda
 }
 
 // blk_begin/blk_end: overlap-save blocks (of V output rows) to transform; blk_end < 0 = all
-int run_col_pass_to_u(blur_b200_plan* p, const float* d_q_chunks, cudaStream_t st, int blk_begin = 0, int blk_end = -1)
+// Fused interleave of the two-factor column kernel (OlsColIO::out).  OFF by default: measured at 16384^2 sigma = 50 it
+// is slower than the separate pass (column + interleave 2.26 ms; fused 3.01 ms with 16-byte stores, 2.59 ms with
+// 32-byte stores): L2 turns over in ~55 us at this kernel's traffic, so the U bytes of the triplet's other two
+// channels are back in DRAM by the time the last CTA arrives (DRAM reads 3.39 -> 4.39 GB, profiles/r02l_*).
+// BLUR_B200_COL_FUSE=1 (read when the plan is created) switches it on for measurements and for its parity test.
+bool col_fuse_enabled(const blur_b200_plan* p) { return p->col_fuse && p->algo == 1 && p->ols_col.R2 && p->d_cnt; }
+
+// d_out != nullptr and a two-factor column axis: the kernel also interleaves (writes d_out, pitch out_cols pixels,
+// ncols valid columns) and *fused is set; otherwise the caller runs run_interleave afterwards.
+int run_col_pass_to_u(blur_b200_plan* p, const float* d_q_chunks, cudaStream_t st, int blk_begin = 0, int blk_end = -1,
+                      uint8_t* d_out = nullptr, int ncols = 0, int out_cols = 0, bool* fused = nullptr)
 {
+    if (fused) *fused = false;
     if (p->algo == 1) {
         OlsColIO io{};
         io.u = p->d_u;
@@ -838,6 +857,10 @@ int run_col_pass_to_u(blur_b200_plan* p, const float* d_q_chunks, cudaStream_t s
         io.nunits = io.ax.R2 ? ols2_col_npairs(io.noct, io.nbl) : io.nbl * 3 * io.noct;
         if (p->quirk_ols) {
             io.corr = p->d_corr_col; io.corr_pitch = p->qpitch;
+        }
+        if (d_out && col_fuse_enabled(p)) {
+            io.out = d_out; io.out_cols = out_cols; io.ncols = std::min(ncols, io.noct * 8); io.cnt = p->d_cnt;
+            if (fused) *fused = true;
         }
         if (io.ax.R2)
             CU_TRY(launch_ols2_col(io, d_q_chunks, p->qpitch, p->nranks * p->stripe_rows, p->d_ols2_tw, p->d_ols2_kt, p->num_sms, st));
@@ -962,7 +985,7 @@ void blur_b200_gauss_plan_destroy(blur_b200_plan* p)
     cudaFree(p->d_ols_twa_row); cudaFree(p->d_ols_twa_col); cudaFree(p->d_ols_twb);
     cudaFree(p->d_ols_kt_row); cudaFree(p->d_ols_kt_col);
     cudaFree(p->d_ols2_tw); cudaFree(p->d_ols2_kt);
-    cudaFree(p->d_q); cudaFree(p->d_u); cudaFree(p->d_corr_row); cudaFree(p->d_corr_col); cudaFree(p->d_insum); cudaFree(p->d_taps);
+    cudaFree(p->d_q); cudaFree(p->d_u); cudaFree(p->d_cnt); cudaFree(p->d_corr_row); cudaFree(p->d_corr_col); cudaFree(p->d_insum); cudaFree(p->d_taps);
     for (uint8_t* b : p->d_sin) cudaFree(b);
     for (uint8_t* b : p->d_sout) cudaFree(b);
     if (p->h2d_stream) cudaStreamDestroy(p->h2d_stream);
@@ -1011,8 +1034,9 @@ int blur_b200_gauss_run_device(blur_b200_plan* p, const uint8_t* d_in, uint8_t* 
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     int rc = run_row_pass(p, d_in, p->d_q, st);
     if (rc) return rc;
-    rc = run_col_pass_to_u(p, p->d_q, st);
-    if (rc) return rc;
+    bool fused = false;
+    rc = run_col_pass_to_u(p, p->d_q, st, 0, -1, d_out, p->cols, p->cols, &fused);
+    if (rc || fused) return rc;
     return run_interleave(p, d_out, p->cols, p->cols, st);
 }
 
@@ -1098,12 +1122,16 @@ int blur_b200_gauss_run_host_batch(blur_b200_plan* p, const uint8_t* const* h_in
         int rows_out = 0;
         for (int b = 0; b < nblk; ++b) {
             const bool last = b + 1 == nblk;
-            int rc = run_col_pass_to_u(p, p->d_q, sc, ols ? b : 0, ols ? (last ? p->ols_col.nblocks : b + 1) : -1);
+            bool fused = false;
+            int rc = run_col_pass_to_u(p, p->d_q, sc, ols ? b : 0, ols ? (last ? p->ols_col.nblocks : b + 1) : -1, p->d_sout[k], p->cols,
+                                       p->cols, &fused);
             if (rc) return rc;
             const int rend = last ? p->rows : std::min(p->rows, (b + 1) * p->ols_col.V) & ~3;
             if (rend <= rows_out) continue;
-            rc = run_interleave(p, p->d_sout[k], p->cols, p->cols, sc, rows_out, rend);
-            if (rc) return rc;
+            if (!fused) {                                   // fused: the column kernel has written these rows of d_sout itself
+                rc = run_interleave(p, p->d_sout[k], p->cols, p->cols, sc, rows_out, rend);
+                if (rc) return rc;
+            }
             CU_TRY(cudaEventRecord(p->ev_out[b], sc));
             CU_TRY(cudaStreamWaitEvent(p->d2h_stream, p->ev_out[b], 0));
             CU_TRY(cudaMemcpyAsync(h_out[i] + rows_out * pitch, p->d_sout[k] + rows_out * pitch, (rend - rows_out) * pitch,
@@ -1463,13 +1491,15 @@ int blur_b200_gauss_col_pass_stage(blur_b200_plan* p, const float* d_q_recv, uin
     io.nunits = ols2_col_npairs(io.noct, io.nbl);
     int col_sms = p->num_sms;
     if (col_ctas_per_sm > 0) col_sms = std::max(1, p->num_sms * std::min(col_ctas_per_sm, ols2_col_ctas_per_sm()) / ols2_col_ctas_per_sm());
-    CU_TRY(launch_ols2_col(io, d_q_recv + stage * plane, w, N * p->stripe_rows, p->d_ols2_tw, p->d_ols2_kt, col_sms, st));
-    ++g_launches;
     const int out_cols = 2 * p->cpp;
     const int valid_cols = std::max(0, std::min(p->cpart, p->cols - p->rank * p->cpart));
     const int ncols = std::max(0, std::min(w, valid_cols - stage * w));
-    if (ncols <= 0) return BLUR_B200_OK;
     uint8_t* out = d_out_cols + static_cast<size_t>(stage) * w * 3;
+    const bool fuse = col_fuse_enabled(p) && ncols > 0;
+    if (fuse) { io.out = out; io.out_cols = out_cols; io.ncols = std::min(ncols, noct * 8); io.cnt = p->d_cnt; }
+    CU_TRY(launch_ols2_col(io, d_q_recv + stage * plane, w, N * p->stripe_rows, p->d_ols2_tw, p->d_ols2_kt, col_sms, st));
+    ++g_launches;
+    if (ncols <= 0 || fuse) return BLUR_B200_OK;
     const int vec = (static_cast<size_t>(out_cols) * 3 % 16 == 0) && (reinterpret_cast<uintptr_t>(out) % 16 == 0) &&
                     (reinterpret_cast<uintptr_t>(u) % 32 == 0) && (p->rows % 4 == 0);
     dim3 g(cdiv(cdiv(noct, 2), 32), cdiv(cdiv(p->rows, 4), 8));
@@ -1484,8 +1514,9 @@ int blur_b200_gauss_col_pass(blur_b200_plan* p, const float* d_q_chunks, uint8_t
     if (!p || !d_q_chunks || !d_out_cols) return BLUR_B200_EINVAL;
     CU_TRY(cudaSetDevice(p->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
-    int rc = run_col_pass_to_u(p, d_q_chunks, st);
-    if (rc) return rc;
+    bool fused = false;
+    int rc = run_col_pass_to_u(p, d_q_chunks, st, 0, -1, d_out_cols, 2 * p->cpp, 2 * p->cpp, &fused);
+    if (rc || fused) return rc;
     return run_interleave(p, d_out_cols, 2 * p->cpp, 2 * p->cpp, st);
 }
 

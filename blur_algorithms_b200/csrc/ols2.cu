@@ -51,13 +51,21 @@ cudaError_t launch_ols2_col(const OlsColIO& io_in, const float* d_q, int qpitch,
     OlsColIO io = io_in;
     io.q = d_q; io.qpitch = qpitch; io.rows_total = rows_total;
     constexpr int smem = ols2_col_smem_bytes<R2>();
-    cudaError_t e = opt_in_smem(ols2_col_kernel<R2>, smem);
+    const bool fuse = io.out != nullptr && io.cnt != nullptr;
+    cudaError_t e = fuse ? opt_in_smem(ols2_col_kernel<R2, true>, smem) : opt_in_smem(ols2_col_kernel<R2, false>, smem);
     if (e != cudaSuccess) return e;
     static const int ctas_env = std::getenv("BLUR_B200_COL_CTAS") ? std::atoi(std::getenv("BLUR_B200_COL_CTAS")) : 0;
     const int per_sm = ctas_env > 0 ? std::min(ctas_env, BLUR_OLS2_COL_CTAS) : BLUR_OLS2_COL_CTAS;
+    if (fuse) {
+        // CTA triplets (one CTA per channel) over the (32-column group, block) items
+        const int ntrip = std::min(io.nunits / 6, std::max(1, num_sms * per_sm / 3));
+        if (ntrip <= 0) return cudaSuccess;
+        ols2_col_kernel<R2, true><<<3 * ntrip, 128, smem, stream>>>(io, tw2, kt);
+        return cudaGetLastError();
+    }
     const int grid = std::min(io.nunits, num_sms * per_sm);       // nunits = (strip, block) pairs, dealt out in contiguous runs
     if (grid <= 0) return cudaSuccess;
-    ols2_col_kernel<R2><<<grid, 128, smem, stream>>>(io, tw2, kt);
+    ols2_col_kernel<R2, false><<<grid, 128, smem, stream>>>(io, tw2, kt);
     return cudaGetLastError();
 }
 

@@ -279,8 +279,69 @@ __device__ __forceinline__ void ols2_col_fetch(const OlsColIO& io, const OlsColI
 
 __device__ __forceinline__ void cp_async_wait_1() { asm volatile("cp.async.wait_group 1;" ::: "memory"); }
 
+// ---- fused interleave ---------------------------------------------------------------------------
+// b g r words (4 pixels each) -> 12 interleaved bytes
+__device__ __forceinline__ void ols2_il4(uint32_t b, uint32_t g, uint32_t r, uint32_t& w0, uint32_t& w1, uint32_t& w2)
+{
+    w0 = __byte_perm(__byte_perm(b, g, 0x1040), r, 0x3410);     // b0 g0 r0 b1
+    w1 = __byte_perm(__byte_perm(g, b, 0x2601), r, 0x3250);     // g1 r1 b2 g2
+    w2 = __byte_perm(__byte_perm(r, b, 0x3072), g, 0x3710);     // r2 b3 g3 r3
+}
+
+// one full 32-byte sector per lane and instruction (STG.256): a store that covers only part of a sector
+// makes L2 fetch the rest from DRAM first, which is what made earlier fusions of the interleave slower
+// than the separate pass
+__device__ __forceinline__ void st_global_256(void* p, const uint32_t* w)
+{
+    asm volatile("st.global.v8.b32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};" ::"l"(p), "r"(w[0]), "r"(w[1]), "r"(w[2]), "r"(w[3]), "r"(w[4]),
+                 "r"(w[5]), "r"(w[6]), "r"(w[7])
+                 : "memory");
+}
+
+// Item (g, b): image rows [r0, r0 + nrows) x columns [32 g, 32 g + 32) of all three channels, U -> out.
+// One thread per row: twelve 8-byte loads (L2: the bytes were written moments ago by this CTA and its two
+// neighbours), byte permutes, three 32-byte stores = three full sectors per row.
+__device__ __forceinline__ void ols2_interleave_item(const OlsColIO& io, int g, int r0, int nrows, int tid)
+{
+    const int c0 = 32 * g;
+    const int noct = io.noct;
+    const size_t plane = static_cast<size_t>(io.rows) * 8;
+    const bool fast = c0 + 32 <= io.ncols && 4 * g + 4 <= noct && (static_cast<size_t>(io.out_cols) * 3) % 32 == 0 &&
+                      reinterpret_cast<uintptr_t>(io.out) % 32 == 0;
+    for (int r = r0 + tid; r < r0 + nrows; r += 128) {
+        if (fast) {
+            uint2 v[3][4];
+#pragma unroll
+            for (int ch = 0; ch < 3; ++ch)
+#pragma unroll
+                for (int o = 0; o < 4; ++o)
+                    v[ch][o] = __ldcg(reinterpret_cast<const uint2*>(io.u + (static_cast<size_t>(ch) * noct + 4 * g + o) * plane + static_cast<size_t>(r) * 8));
+            uint32_t w[24];
+#pragma unroll
+            for (int o = 0; o < 4; ++o) {
+                ols2_il4(v[0][o].x, v[1][o].x, v[2][o].x, w[6 * o + 0], w[6 * o + 1], w[6 * o + 2]);
+                ols2_il4(v[0][o].y, v[1][o].y, v[2][o].y, w[6 * o + 3], w[6 * o + 4], w[6 * o + 5]);
+            }
+            uint8_t* d = io.out + (static_cast<size_t>(r) * io.out_cols + c0) * 3;
+#pragma unroll
+            for (int k = 0; k < 3; ++k) st_global_256(d + 32 * k, w + 8 * k);
+        } else {
+            for (int o = 0; o < 4 && 4 * g + o < noct; ++o)
+                for (int px = 0; px < 8; ++px) {
+                    const int c = c0 + 8 * o + px;
+                    if (c >= io.ncols) break;
+                    for (int ch = 0; ch < 3; ++ch)
+                        io.out[(static_cast<size_t>(r) * io.out_cols + c) * 3 + ch] =
+                            __ldcg(io.u + (static_cast<size_t>(ch) * noct + 4 * g + o) * plane + static_cast<size_t>(r) * 8 + px);
+                }
+        }
+    }
+}
+
 // io.nunits = ols2_col_npairs(noct, nbl) (strip, block) pairs, walked in the order Ols2ColWalk::at gives
-template <int R2>
+// FUSE: CTA triplets (blockIdx.x = 3 * triplet + channel) walk runs of (group, block) items, the two octet pairs
+// of a group back to back; the triplet's last arriver interleaves the item (see OlsColIO::out).  gridDim.x % 3 == 0.
+template <int R2, bool FUSE>
 __global__ void __launch_bounds__(128, BLUR_OLS2_COL_CTAS)
 ols2_col_kernel(const __grid_constant__ OlsColIO io, const float2* __restrict__ tw2_, const float* __restrict__ kt)
 {
@@ -297,8 +358,27 @@ ols2_col_kernel(const __grid_constant__ OlsColIO io, const float2* __restrict__ 
     const uint64_t pol = l2_policy_evict_last();
     // this CTA's run of pairs
     const long long np = io.nunits;
-    const int q0 = static_cast<int>(np * blockIdx.x / gridDim.x), q1 = static_cast<int>(np * (blockIdx.x + 1) / gridDim.x);
-    Ols2ColWalk cur = Ols2ColWalk::at(q0, io.nbl), nxt = Ols2ColWalk::at(q0 + 1, io.nbl);
+    int q0, q1;
+    int fch = 0;                                          // FUSE: this CTA's channel
+    __shared__ int s_last;
+    if (FUSE) {
+        // items m = g * nbl + b, nitems = nunits / 6; pair index within the CTA's run: q = 2 * m + h
+        const int trip = blockIdx.x / 3, ntrip = gridDim.x / 3;
+        const long long nitems = np / 6;
+        fch = blockIdx.x - 3 * trip;
+        q0 = 2 * static_cast<int>(nitems * trip / ntrip);
+        q1 = 2 * static_cast<int>(nitems * (trip + 1) / ntrip);
+    } else {
+        q0 = static_cast<int>(np * blockIdx.x / gridDim.x);
+        q1 = static_cast<int>(np * (blockIdx.x + 1) / gridDim.x);
+    }
+    // FUSE walk: pair q -> item m = q >> 1 = g * nbl + b, octet pair 2 g + (q & 1), this CTA's channel
+    auto walk = [&](int q) {
+        if (!FUSE) return Ols2ColWalk::at(q, io.nbl);
+        const int m = q >> 1, g = m / io.nbl, b = m - g * io.nbl;
+        return Ols2ColWalk{3 * (2 * g + (q & 1)) + fch, b};
+    };
+    Ols2ColWalk cur = walk(q0), nxt = walk(q0 + 1);
     // prologue: both members of the first pair
 #pragma unroll
     for (int m = 0; m < 2; ++m) {
@@ -338,8 +418,24 @@ ols2_col_kernel(const __grid_constant__ OlsColIO io, const float2* __restrict__ 
             cp_async_commit();
             if (ctx.valid) ols2_col_pass3_store<R2>(io, ctx, X, t, x, w);
         }
+        if (FUSE && (q & 1)) {
+            // this channel of item m is complete: publish, and interleave the item if the other two channels are too
+            const int m = q >> 1, g = m / io.nbl, b = m - g * io.nbl;
+            __threadfence();                               // this thread's U bytes are visible device-wide ...
+            __syncthreads();                               // ... for every thread of the CTA
+            if (tid == 0) s_last = atomicAdd(io.cnt + m, 1) == 2;
+            __syncthreads();
+            if (s_last) {
+                __threadfence();
+                const int blk = io.b0 + b;
+                const int r0 = blk * io.ax.V;
+                const int nrows = io.rows - r0 < io.ax.V ? io.rows - r0 : io.ax.V;
+                ols2_interleave_item(io, g, r0, nrows, tid);
+                if (tid == 0) io.cnt[m] = 0;               // ready for the next launch
+            }
+        }
         cur = nxt;
-        nxt = Ols2ColWalk::at(q + 2, io.nbl);
+        nxt = walk(q + 2);
     }
 }
 

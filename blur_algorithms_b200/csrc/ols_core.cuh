@@ -434,6 +434,13 @@ struct OlsColIO {
     int nbl;               // blocks in this launch (two-factor kernel: nunits = nbl * 3 * ceil(noct / 2) strip-block pairs)
     const float* corr;     // pffft Nyquist quirk, see OlsRowIO::corr: corr[ch * corr_pitch + column]
     int corr_pitch;
+    // Fused interleave (two-factor kernel, ols2_col_kernel<R2, true>): CTA triplets take the three channels of the
+    // same (32-column group, block) items; the CTA that finishes an item last (cnt[item] counts arrivals) reads the
+    // three channels' U bytes back from L2 and writes the interleaved BGR rows of `out` (pitch out_cols pixels,
+    // ncols valid columns): the separate interleave pass and its U read from DRAM disappear.
+    uint8_t* out;
+    int out_cols, ncols;
+    int* cnt;              // one zero-initialised counter per item; the last arriver resets it
 
     struct Ctx {
         uint8_t* ua;       // U byte of (ch, oct, row 0, 0)

@@ -576,6 +576,25 @@ def test_layout_templates_other_types(bb, torch):
     assert torch.equal(t, img.permute(1, 0, 2).contiguous())
 
 
+@pytest.mark.gpu
+def test_gauss_fused_interleave_variant_bit_identical(bb, torch, monkeypatch):
+    """BLUR_B200_COL_FUSE=1: the column kernel's last-arriver interleave (measured slower than the separate pass,
+    kept as a knob) writes exactly the bytes of column pass + interleave_oct_kernel, ragged sizes included."""
+    for rows, cols, sigma in [(1080, 1920, 5.0), (700, 1000, 9.0), (2160, 3840, 25.0), (333, 1531, 3.0), (4096, 4100, 50.0)]:
+        d = torch.from_numpy(synth("noise", rows, cols, 8)).cuda()
+        monkeypatch.delenv("BLUR_B200_COL_FUSE", raising=False)
+        monkeypatch.setenv("BLUR_B200_OLS2", "1")
+        p0 = bb.GaussPlan(rows, cols, sigma, 0)
+        a = p0.run(d, torch.empty_like(d))
+        monkeypatch.setenv("BLUR_B200_COL_FUSE", "1")
+        p1 = bb.GaussPlan(rows, cols, sigma, 0)
+        b = p1.run(d, torch.empty_like(d))
+        b2 = p1.run(d, torch.empty_like(d))                # counters were reset by the last arrivers
+        torch.cuda.synchronize()
+        assert torch.equal(a, b) and torch.equal(a, b2), (rows, cols, sigma)
+        p0.close(); p1.close()
+
+
 # ---------------------------------------------------------------- FFT box blur (`#define boxblur`)
 
 @pytest.mark.gpu
