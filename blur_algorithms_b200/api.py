@@ -205,6 +205,30 @@ class GaussPlan:
     def col_pass(self, d_q_chunks, d_out_cols, stream: int | None = None):
         check(lib.blur_b200_gauss_col_pass(self._h, _ptr(d_q_chunks), _ptr(d_out_cols), _stream() if stream is None else stream))
 
+    # pffft-mode sharded plans (blur_b200_gauss_quirk_* in include/blur_b200.h)
+    def quirk_buffers(self):
+        """(corr_row, insum): zero-copy torch views of the plan's two correction buffers (float32 [3*rows],
+        int32 [nseg*3*cols]) that a sharded caller sums over the ranks between quirk_local and quirk_finish;
+        None for plans without the overlap-save Nyquist corrections."""
+        import torch
+        pc, pi = C.c_void_p(), C.c_void_p()
+        nc, ni = C.c_int64(), C.c_int64()
+        if lib.blur_b200_gauss_quirk_buffers(self._h, C.byref(pc), C.byref(nc), C.byref(pi), C.byref(ni)) != _lib.OK:
+            return None
+
+        class _Dev:                                    # __cuda_array_interface__ wrapper around a raw device pointer
+            def __init__(self, ptr, n, typestr):
+                self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+        return (torch.as_tensor(_Dev(pc.value, nc.value, "<f4"), device="cuda"),
+                torch.as_tensor(_Dev(pi.value, ni.value, "<i4"), device="cuda"))
+
+    def quirk_local(self, d_in_stripe, stream: int | None = None):
+        check(lib.blur_b200_gauss_quirk_local(self._h, _ptr(d_in_stripe) if d_in_stripe is not None else None,
+                                              _stream() if stream is None else stream))
+
+    def quirk_finish(self, stream: int | None = None):
+        check(lib.blur_b200_gauss_quirk_finish(self._h, _stream() if stream is None else stream))
+
     # staged exchange (blur_b200_gauss_row_pass_staged & co. in include/blur_b200.h)
     def staged_supported(self, nstages: int) -> bool:
         return lib.blur_b200_gauss_staged_supported(self._h, int(nstages)) == _lib.OK

@@ -302,10 +302,13 @@ constexpr int kQuirkSeg = 64;      // maximum; a launch uses nseg = clamp(rows /
 // byte columns j of the interleaved image: partial[seg][j] = sum over the segment's rows of w_r (-1)^r in[r][j].
 // grid (ceil(pitch/4/128), kQuirkSeg), 128 threads, one 32-bit word column per thread (vec) or one byte column.
 __global__ void __launch_bounds__(128)
-quirk_insum_partial(const uint8_t* __restrict__ in, int rows, int pitch /* cols*3 */, int pad, int* __restrict__ partial, int vec)
+quirk_insum_partial(const uint8_t* __restrict__ in_local, int rows, int pitch /* cols*3 */, int pad, int* __restrict__ partial, int vec,
+                    int row0 /* image row of in_local's first row */, int nlocal /* rows present */)
 {
-    const int seg_rows = (rows + gridDim.y - 1) / gridDim.y;
-    const int r_begin = blockIdx.y * seg_rows, r_end = min(rows, r_begin + seg_rows);
+    // segments cut the LOCAL rows; weights and parities use the image row index (a sharded plan holds a stripe)
+    const int seg_rows = (nlocal + gridDim.y - 1) / gridDim.y;
+    const int r_begin = row0 + blockIdx.y * seg_rows, r_end = min(row0 + nlocal, r_begin + seg_rows);
+    const uint8_t* in = in_local - static_cast<ptrdiff_t>(row0) * pitch;
     const int j = (blockIdx.x * 128 + threadIdx.x) * (vec ? 4 : 1);
     if (j >= pitch) return;
     int* out = partial + static_cast<size_t>(blockIdx.y) * pitch + j;
@@ -332,11 +335,12 @@ quirk_insum_partial(const uint8_t* __restrict__ in, int rows, int pitch /* cols*
 // in shared memory (dynamic, (128 + 2 pad) ints).
 __global__ void __launch_bounds__(128)
 quirk_col_corr(const int* __restrict__ partial, int cols, int rows, int pad, const double* __restrict__ taps /* [pad+1] */,
-               const float* __restrict__ corr_row, double c, float* __restrict__ corr, int qpitch, int nseg)
+               const float* __restrict__ corr_row, double c, float* __restrict__ corr, int qpitch, int nseg,
+               int xoff /* image column of corr[.][0]: a sharded plan corrects its own column part */, int xend)
 {
     extern __shared__ int sS[];
     __shared__ double red[128];
-    const int tid = threadIdx.x, ch = blockIdx.y, x0 = blockIdx.x * 128;
+    const int tid = threadIdx.x, ch = blockIdx.y, x0 = xoff + blockIdx.x * 128;
     const int pitch = cols * 3;
     const float* cr = corr_row + static_cast<size_t>(ch) * rows;
     double a = 0;
@@ -359,11 +363,11 @@ quirk_col_corr(const int* __restrict__ partial, int cols, int rows, int pad, con
         __syncthreads();
     }
     const int x = x0 + tid;
-    if (x >= cols) return;
+    if (x >= cols || x >= xend) return;
     double acc = taps[0] * static_cast<double>(sS[tid + pad]);
     for (int k = 1; k <= pad; ++k) acc += taps[k] * (static_cast<double>(sS[tid + pad - k]) + static_cast<double>(sS[tid + pad + k]));
     acc += ((x & 1) ? -1.0 : 1.0) * red[0];
-    corr[static_cast<size_t>(ch) * qpitch + x] = static_cast<float>(c * acc);
+    corr[static_cast<size_t>(ch) * qpitch + (x - xoff)] = static_cast<float>(c * acc);
 }
 
 // ------------------------------------------------------------------ exchange kernel
@@ -777,18 +781,53 @@ int row_wave_pairs(const blur_b200_plan* p)
 
 // pffft-quirk plans: column corrections from the input image and the row corrections (all rows of
 // d_corr_row must have been produced on `st` before)
+// row segments of the integer column sums: the same count on every rank of a sharded plan (the partials are
+// summed element-wise across the ranks)
+int quirk_nseg(const blur_b200_plan* p) { return std::max(1, std::min(kQuirkSeg, p->stripe_rows / 128)); }
+
+// local half: per-row corrections of this plan's rows (into d_corr_row at their image row index) and the partial
+// integer column sums over them.  A sharded plan's caller then sums d_corr_row and d_insum over the ranks.
+int quirk_local(blur_b200_plan* p, const uint8_t* d_in_stripe, cudaStream_t st)
+{
+    if (p->nranks > 1) CU_TRY(cudaMemsetAsync(p->d_corr_row, 0, sizeof(float) * 3 * p->rows, st));
+    const int pitch = p->cols * 3;
+    const int vec = pitch % 4 == 0 && reinterpret_cast<uintptr_t>(d_in_stripe) % 4 == 0;
+    const int nseg = quirk_nseg(p);
+    if (p->valid_rows > 0) {
+        quirk_rows_kernel<<<p->valid_rows, 128, 0, st>>>(d_in_stripe, p->cols, p->gg.pad, p->quirk_c_row, p->d_corr_row + p->row0, p->rows, vec);
+        CU_TRY(cudaGetLastError());
+        ++g_launches;
+    }
+    quirk_insum_partial<<<dim3(cdiv(vec ? pitch / 4 : pitch, 128), nseg), 128, 0, st>>>(d_in_stripe, p->rows, pitch, p->gg.pad, p->d_insum, vec,
+                                                                                       p->row0, std::max(0, p->valid_rows));
+    CU_TRY(cudaGetLastError());
+    ++g_launches;
+    return BLUR_B200_OK;
+}
+
+// second half: column corrections of this plan's column part from the (summed) d_insum and d_corr_row
+int quirk_finish(blur_b200_plan* p, cudaStream_t st)
+{
+    const int xoff = p->nranks > 1 ? p->rank * p->cpart : 0;
+    const int xend = p->nranks > 1 ? std::min(p->cols, xoff + p->cpart) : p->cols;
+    if (xend <= xoff) return BLUR_B200_OK;
+    quirk_col_corr<<<dim3(cdiv(xend - xoff, 128), 3), 128, sizeof(int) * (128 + 2 * p->gg.pad), st>>>(
+        p->d_insum, p->cols, p->rows, p->gg.pad, p->d_taps, p->d_corr_row, p->quirk_c_col, p->d_corr_col, p->qpitch, quirk_nseg(p), xoff, xend);
+    CU_TRY(cudaGetLastError());
+    ++g_launches;
+    return BLUR_B200_OK;
+}
+
+// single-GPU plans: both halves back to back (all rows of d_corr_row must have been produced on `st` before)
 int quirk_prepare_cols(blur_b200_plan* p, const uint8_t* d_in, cudaStream_t st)
 {
     const int pitch = p->cols * 3;
     const int vec = pitch % 4 == 0 && reinterpret_cast<uintptr_t>(d_in) % 4 == 0;
-    const int nseg = std::max(1, std::min(kQuirkSeg, p->rows / 128));
-    quirk_insum_partial<<<dim3(cdiv(vec ? pitch / 4 : pitch, 128), nseg), 128, 0, st>>>(d_in, p->rows, pitch, p->gg.pad, p->d_insum, vec);
+    quirk_insum_partial<<<dim3(cdiv(vec ? pitch / 4 : pitch, 128), quirk_nseg(p)), 128, 0, st>>>(d_in, p->rows, pitch, p->gg.pad, p->d_insum, vec,
+                                                                                                0, p->rows);
     CU_TRY(cudaGetLastError());
-    quirk_col_corr<<<dim3(cdiv(p->cols, 128), 3), 128, sizeof(int) * (128 + 2 * p->gg.pad), st>>>(
-        p->d_insum, p->cols, p->rows, p->gg.pad, p->d_taps, p->d_corr_row, p->quirk_c_col, p->d_corr_col, p->qpitch, nseg);
-    CU_TRY(cudaGetLastError());
-    g_launches += 2;
-    return BLUR_B200_OK;
+    ++g_launches;
+    return quirk_finish(p, st);
 }
 
 int run_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, float* d_q, cudaStream_t st, float* const* peers = nullptr)
@@ -802,7 +841,7 @@ int run_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, float* d_q, cuda
         io.srows = p->stripe_rows; io.qpitch = p->qpitch; io.cpart = p->cpart; io.nparts = p->nranks;
         io.ax = p->ols_row;
         io.nunits = io.ax.nblocks * io.npairs;
-        if (p->quirk_ols) {
+        if (p->quirk_ols && p->nranks == 1) {
             quirk_rows_kernel<<<p->valid_rows, 128, 0, st>>>(d_in_stripe, p->cols, p->gg.pad, p->quirk_c_row, p->d_corr_row, p->rows,
                                                              p->cols % 4 == 0 && reinterpret_cast<uintptr_t>(d_in_stripe) % 4 == 0);
             CU_TRY(cudaGetLastError());
@@ -810,6 +849,9 @@ int run_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, float* d_q, cuda
             io.corr = p->d_corr_row; io.corr_pitch = p->rows;
             const int rc = quirk_prepare_cols(p, d_in_stripe, st);
             if (rc) return rc;
+        } else if (p->quirk_ols) {
+            // sharded: blur_b200_gauss_quirk_local has produced this stripe's rows (the kernel indexes stripe rows)
+            io.corr = p->d_corr_row + p->row0; io.corr_pitch = p->rows;
         }
         if (peers && p->nranks > 1) {
             io.peer = 1; io.rank = p->rank;
@@ -1234,7 +1276,7 @@ int blur_b200_gauss_row_pass(blur_b200_plan* p, const uint8_t* d_in_stripe, floa
 int blur_b200_gauss_row_pass_peer(blur_b200_plan* p, const uint8_t* d_in_stripe, float* const* q_peers, int npeers, void* stream)
 {
     if (!p || !d_in_stripe || !q_peers || npeers != p->nranks || npeers > OlsRowIO::kMaxPeers) return BLUR_B200_EINVAL;
-    if (p->algo != 1 || p->quirk_ols) return BLUR_B200_ESIZE;      // only the overlap-save row kernel has the fused epilogue
+    if (p->algo != 1) return BLUR_B200_ESIZE;      // only the overlap-save row kernel has the fused epilogue
     for (int k = 0; k < npeers; ++k)
         if (!q_peers[k]) return BLUR_B200_EINVAL;
     CU_TRY(cudaSetDevice(p->device));
@@ -1245,7 +1287,7 @@ int blur_b200_gauss_row_pass_push(blur_b200_plan* p, const uint8_t* d_in_stripe,
                                   int nchunks, void* stream)
 {
     if (!p || !d_in_stripe || !q_peers || npeers != p->nranks || npeers > OlsRowIO::kMaxPeers) return BLUR_B200_EINVAL;
-    if (p->algo != 1 || p->quirk_ols) return BLUR_B200_ESIZE;
+    if (p->algo != 1) return BLUR_B200_ESIZE;
     for (int k = 0; k < npeers; ++k)
         if (!q_peers[k]) return BLUR_B200_EINVAL;
     if (p->valid_rows <= 0) return BLUR_B200_OK;
@@ -1293,6 +1335,7 @@ int blur_b200_gauss_row_pass_push(blur_b200_plan* p, const uint8_t* d_in_stripe,
         io.ax = p->ols_row;
         io.nunits = io.ax.nblocks * io.npairs;
         io.peer = 1; io.rank = rank;
+        if (p->quirk_ols) { io.corr = p->d_corr_row + p->row0 + r0; io.corr_pitch = p->rows; }
         for (int part = 0; part < N; ++part) io.qpeer[part] = base[part] + static_cast<size_t>(r0) * p->qpitch;
         static const int diag = std::getenv("BLUR_B200_PUSH_DIAG") ? std::atoi(std::getenv("BLUR_B200_PUSH_DIAG")) : 0;   // timing experiments only
         if (diag != 1) {
@@ -1346,6 +1389,37 @@ int blur_b200_gauss_row_pass_push(blur_b200_plan* p, const uint8_t* d_in_stripe,
     return BLUR_B200_OK;
 }
 
+// ---- pffft Nyquist quirk of a SHARDED overlap-save plan (Source.cpp:414-427) --------------------------
+// Row corrections are local to a stripe; the column corrections need sums over ALL rows: the integer column sums of
+// the input (d_insum partials) and the row corrections themselves (d_corr_row).  Sequence per blur on every rank:
+//   blur_b200_gauss_quirk_local  ->  row pass (+ exchange)  ->  caller sums both buffers over the ranks
+//   (all-reduce SUM; every element of d_corr_row is non-zero on one rank only, d_insum is integer: exact)
+//   ->  blur_b200_gauss_quirk_finish  ->  column pass.
+int blur_b200_gauss_quirk_buffers(blur_b200_plan* p, float** d_corr_row, int64_t* n_corr_row, int** d_insum, int64_t* n_insum)
+{
+    if (!p || !d_corr_row || !n_corr_row || !d_insum || !n_insum) return BLUR_B200_EINVAL;
+    if (!p->quirk_ols) return BLUR_B200_ESIZE;
+    *d_corr_row = p->d_corr_row; *n_corr_row = static_cast<int64_t>(3) * p->rows;
+    *d_insum = p->d_insum; *n_insum = static_cast<int64_t>(quirk_nseg(p)) * 3 * p->cols;
+    return BLUR_B200_OK;
+}
+
+int blur_b200_gauss_quirk_local(blur_b200_plan* p, const uint8_t* d_in_stripe, void* stream)
+{
+    if (!p || (!d_in_stripe && p->valid_rows > 0)) return BLUR_B200_EINVAL;
+    if (!p->quirk_ols) return BLUR_B200_ESIZE;
+    CU_TRY(cudaSetDevice(p->device));
+    return quirk_local(p, d_in_stripe, static_cast<cudaStream_t>(stream));
+}
+
+int blur_b200_gauss_quirk_finish(blur_b200_plan* p, void* stream)
+{
+    if (!p) return BLUR_B200_EINVAL;
+    if (!p->quirk_ols) return BLUR_B200_ESIZE;
+    CU_TRY(cudaSetDevice(p->device));
+    return quirk_finish(p, static_cast<cudaStream_t>(stream));
+}
+
 // ---- staged exchange ------------------------------------------------------------------------------
 // The part of every rank (cpart columns) is cut into `nstages` sub-ranges of w = cpart / nstages columns.
 // Stage k of the row pass transforms, for all rows of the stripe, the overlap-save blocks that touch
@@ -1359,7 +1433,7 @@ namespace {
 int staged_check(const blur_b200_plan* p, int nstages)
 {
     if (!p || nstages < 1 || nstages > blur_b200_plan::kMaxStages) return BLUR_B200_EINVAL;
-    if (p->algo != 1 || p->quirk_ols || !p->ols_row.R2 || !p->ols_col.R2) return BLUR_B200_ESIZE;
+    if (p->algo != 1 || !p->ols_row.R2 || !p->ols_col.R2) return BLUR_B200_ESIZE;
     if (p->cpart % (16 * nstages) != 0) return BLUR_B200_ESIZE;            // whole octet pairs per sub-range
     const int w = p->cpart / nstages;
     if (p->nranks * nstages > OlsRowIO::kMaxParts || p->ols_row.nblocks > OlsRowIO::kMaxSel) return BLUR_B200_ESIZE;
@@ -1423,6 +1497,7 @@ int blur_b200_gauss_row_pass_staged(blur_b200_plan* p, const uint8_t* d_in_strip
         io.srows = p->stripe_rows; io.qpitch = w; io.cpart = w; io.nparts = N * S; io.chparts = N;
         io.ax = p->ols_row;
         io.peer = 1; io.rank = rank;
+        if (p->quirk_ols) { io.corr = p->d_corr_row + p->row0; io.corr_pitch = p->rows; }
         // virtual part v = (destination d, sub-range kk): own part straight into the own receive buffer, the others
         // into the send buffer at the source-block slot of the destination (the kernel adds rank * blk)
         // (store mode: every part straight into its owner's receive buffer through bulk copies over NVLink)
@@ -1489,6 +1564,7 @@ int blur_b200_gauss_col_pass_stage(blur_b200_plan* p, const float* d_q_recv, uin
     io.b0 = 0;
     io.nbl = io.ax.nblocks;
     io.nunits = ols2_col_npairs(io.noct, io.nbl);
+    if (p->quirk_ols) { io.corr = p->d_corr_col + stage * w; io.corr_pitch = p->qpitch; }
     int col_sms = p->num_sms;
     if (col_ctas_per_sm > 0) col_sms = std::max(1, p->num_sms * std::min(col_ctas_per_sm, ols2_col_ctas_per_sm()) / ols2_col_ctas_per_sm());
     const int out_cols = 2 * p->cpp;

@@ -73,8 +73,14 @@ inline ShardGeom shard_geometry(const GaussGeometry& gg, int nyquist_mode, int r
     const int rows = gg.rows, cols = gg.cols;
     // Overlap-save unless the kernel is too wide for the block menu.  The Nyquist quirk of pffft
     // (defined on the reference's full-length tile) is a rank-one correction per line that the
-    // overlap-save epilogues add on a single GPU; the sharded plan keeps the full-length kernel.
-    int want_ols = (nyquist_mode == 0 || nranks == 1) ? 1 : 0;
+    // overlap-save epilogues add; in a sharded plan the caller sums the two small correction
+    // buffers over the ranks (blur_b200_gauss_quirk_local / _finish).  BLUR_B200_QUIRK_SHARDED=full
+    // keeps round 1's full-length kernel for sharded pffft-mode plans.
+    int want_ols = 1;
+    if (nyquist_mode != 0 && nranks > 1) {
+        const char* q = std::getenv("BLUR_B200_QUIRK_SHARDED");
+        if (q && !std::strcmp(q, "full")) want_ols = 0;
+    }
     if (const char* e = std::getenv("BLUR_B200_ALGO")) {
         if (!std::strcmp(e, "full")) want_ols = 0;
     }

@@ -204,7 +204,9 @@ class ShardedGaussBlur:
         if self.symm is None:
             self.q_send = torch.zeros(nfl, dtype=torch.float32, device=self.device)
             self.q_recv = torch.zeros_like(self.q_send)
-        self.out_cols = torch.zeros((rows, 2 * g.cpp, 3), dtype=torch.uint8, device=self.device)
+        # [nranks * stripe_rows] rows so that the optional return exchange can send equal blocks; the blur uses the first `rows`
+        self._out_store = torch.zeros((self.nranks * g.stripe_rows, 2 * g.cpp, 3), dtype=torch.uint8, device=self.device)
+        self.out_cols = self._out_store[:rows]
         if row_pass is None or col_pass is None:
             from .api import GaussPlan
             self.plan = GaussPlan(rows, cols, sigma, nyquist_mode, device=self.device.index or 0,
@@ -212,6 +214,10 @@ class ShardedGaussBlur:
             row_pass = self.plan.row_pass
             col_pass = self.plan.col_pass
         self._row_pass, self._col_pass = row_pass, col_pass
+        # pffft mode on the overlap-save path: two small correction buffers are summed over the ranks per blur
+        self._quirk = self.plan.quirk_buffers() if (self.plan is not None and nyquist_mode != 0 and g.algo == 1 and self.nranks > 1) else None
+        if self._quirk is not None and self.exchange_mode == "sstore":
+            self.exchange_mode = "staged"                # the second stream would not see quirk_finish
         if self.exchange_mode in ("staged", "sstore"):
             # fewer stages if the part does not divide, plain push if the plan cannot run staged at all
             while self.nstages > 1 and not (self.plan is not None and self.symm is not None and self.plan.staged_supported(self.nstages)):
@@ -267,15 +273,44 @@ class ShardedGaussBlur:
         else:
             self._col_pass(self.q_recv, self.out_cols)
 
-    def run(self, in_stripe: torch.Tensor) -> torch.Tensor:
+    def run(self, in_stripe: torch.Tensor, row_sharded: bool = False) -> torch.Tensor:
         """in_stripe: uint8 [valid_rows, cols, 3] (this rank's rows).  Returns this rank's column
-        stripe of the result, uint8 [rows, valid_cols, 3] (a view into an internal buffer)."""
+        stripe of the result, uint8 [rows, valid_cols, 3] (a view into an internal buffer) — or, with
+        row_sharded=True, this rank's ROW stripe [valid_rows, cols, 3] after the return exchange."""
         self._rows(in_stripe)
-        return self._cols()
+        out = self._cols()
+        return self.to_row_stripe() if row_sharded else out
+
+    def to_row_stripe(self) -> torch.Tensor:
+        """Return exchange (optional): the uint8 result goes back from column stripes to the row stripes
+        the input came in (3 B/px, a quarter of the float32 exchange), one all-to-all of equal blocks
+        [stripe_rows][2*cpp][3]; the output of one sharded blur can then feed the next.  A collective call
+        (NCCL / gloo all_to_all), not a hot-path kernel."""
+        g, n = self.geom, self.nranks
+        if n == 1:
+            return self.out_cols[: g.valid_rows, : g.cols]
+        send = self._out_store.view(n, g.stripe_rows, 2 * g.cpp, 3)
+        if not hasattr(self, "_ret_recv"):
+            self._ret_recv = torch.empty_like(send)
+        _all_to_all(send.view(-1), self._ret_recv.view(-1), n, self.group)
+        rows_here = max(g.valid_rows, 0)
+        # block s holds this rank's rows x rank s' columns
+        return self._ret_recv.permute(1, 0, 2, 3).reshape(g.stripe_rows, n * 2 * g.cpp, 3)[:rows_here, : g.cols].contiguous()
+
+    def _quirk_sum(self) -> None:
+        """pffft-mode sharded plans: the column corrections need the row corrections and the integer column sums of ALL
+        rows — all-reduce the two small buffers (exact: disjoint non-zeros / integers), then finish on this rank's columns."""
+        if self._quirk is None:
+            return
+        for t in self._quirk:
+            dist.all_reduce(t, op=dist.ReduceOp.SUM, group=self.group)
+        self.plan.quirk_finish()
 
     def _rows(self, in_stripe: torch.Tensor) -> None:
         """row pass of this rank's stripe + the exchange (the distributed flip_block, Source.cpp:540)"""
         self._last_in = in_stripe
+        if self._quirk is not None:
+            self.plan.quirk_local(in_stripe if self.geom.valid_rows > 0 else None)
         if self.symm is not None:
             # peers may still be reading their buffers (previous blur's column pass)
             self.symm.barrier(channel=0)
@@ -304,6 +339,7 @@ class ShardedGaussBlur:
     def _cols(self, after=None) -> torch.Tensor:
         """`after`: an event the column passes must also wait for (the streamed host path: the previous image's
         download has left out_cols)."""
+        self._quirk_sum()
         sstore = self.symm is not None and self.exchange_mode == "sstore"
         main = torch.cuda.current_stream(self.device) if (sstore or after is not None) else None
         if after is not None and not sstore:

@@ -145,6 +145,16 @@ int blur_b200_gauss_row_pass_peer(blur_b200_plan *plan, const uint8_t *d_in_stri
 int blur_b200_gauss_row_pass_push(blur_b200_plan *plan, const uint8_t *d_in_stripe, float *const *q_peers, int npeers,
                                   int nchunks, void *stream);
 
+/* pffft-mode (BLUR_B200_NYQUIST_PFFFT) SHARDED overlap-save plans: the Nyquist quirk of Source.cpp:414-427 is a
+ * per-line correction; a stripe's row corrections are local, the column corrections need two small sums over all
+ * rows.  Per blur on every rank: blur_b200_gauss_quirk_local(stripe) -> row pass (any exchange entry above) ->
+ * the caller all-reduces (SUM) the two buffers blur_b200_gauss_quirk_buffers returns (3*rows floats, of which
+ * every element is non-zero on one rank only, and nseg*3*cols ints: the sums are exact) ->
+ * blur_b200_gauss_quirk_finish -> column pass.  Single-GPU plans do all of this inside the row pass. */
+int blur_b200_gauss_quirk_buffers(blur_b200_plan *plan, float **d_corr_row, int64_t *n_corr_row, int **d_insum, int64_t *n_insum);
+int blur_b200_gauss_quirk_local(blur_b200_plan *plan, const uint8_t *d_in_stripe, void *stream);
+int blur_b200_gauss_quirk_finish(blur_b200_plan *plan, void *stream);
+
 /* Staged exchange (two-factor overlap-save plans, nranks <= 8): the exchange hidden behind BOTH FFT passes.
  * Every rank's part (2*cpp columns) is cut into `nstages` column sub-ranges of w = 2*cpp / nstages columns.  The
  * row pass runs as nstages launches; launch k transforms, for every row of the stripe, the overlap-save blocks that

@@ -239,10 +239,14 @@ def test_gauss_errors(bb):
         bb.GaussPlan(64, 64, -1.0)
 
 
-def test_gauss_sharded_emulated_on_one_gpu(bb, torch):
+def test_gauss_sharded_emulated_on_one_gpu(bb, torch, monkeypatch):
     """P ranks' plans executed one after another on one GPU with the all-to-all done by copies:
     bit-identical to the single-plan result (SURVEY.md §4 multi-GPU test plan)."""
     for rows, cols, sigma, mode, P in [(135, 241, 6.0, 1, 3), (240, 320, 5.0, 0, 2), (256, 256, 3.0, 0, 8)]:
+        if mode == 1:
+            monkeypatch.setenv("BLUR_B200_QUIRK_SHARDED", "full")      # round 1's sharded pffft path: the full-length kernel
+        else:
+            monkeypatch.delenv("BLUR_B200_QUIRK_SHARDED", raising=False)
         img = synth("noise", rows, cols, 6)
         single = torch.from_numpy(img).cuda()
         p1 = bb.GaussPlan(rows, cols, sigma, mode)
@@ -269,7 +273,8 @@ def test_gauss_sharded_emulated_on_one_gpu(bb, torch):
         if mode == 0:
             assert torch.equal(full, single), (rows, cols, P)
         else:
-            # single GPU: overlap-save blocks + Nyquist correction; sharded: full-length kernel
+            # pffft mode without the cross-rank sums of test_gauss_sharded_pffft_mode_emulated_on_one_gpu is only
+            # meaningful on the full-length kernel (BLUR_B200_QUIRK_SHARDED=full, set below for this case)
             assert (full.int() - single.int()).abs().max().item() <= 1, (rows, cols, P)
         for pl in plans + [p1]:
             pl.close()
@@ -574,6 +579,69 @@ def test_layout_templates_other_types(bb, torch):
     t = torch.empty((53, 37, 3), dtype=torch.uint8, device="cuda")
     bb.flip_block(img, t, 53, 37, channels=3)
     assert torch.equal(t, img.permute(1, 0, 2).contiguous())
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("mode_name", ["staged", "peer", "push", "plain"])
+def test_gauss_sharded_pffft_mode_emulated_on_one_gpu(bb, torch, mode_name):
+    """pffft_ semantics (Nyquist quirk, Source.cpp:414-427) of a SHARDED plan on the overlap-save kernels: row
+    corrections per stripe, the two small correction buffers summed over the ranks (here: by hand, all ranks in one
+    process), column corrections per column part.  Bit-identical to the single-GPU pffft-mode plan."""
+    for rows, cols, sigma, P, S in [(1080, 4096, 50.0, 2, 4), (700, 4096, 30.0, 4, 2), (333, 8192, 50.0, 8, 2), (1001, 1531, 9.0, 4, 2)]:
+        img = synth("noise", rows, cols, 12)
+        single = torch.from_numpy(img).cuda()
+        p1 = bb.GaussPlan(rows, cols, sigma, 1)
+        p1.run(single)
+        plans = [bb.GaussPlan(rows, cols, sigma, 1, rank=r, nranks=P) for r in range(P)]
+        assert plans[0].info["algo"] == 1
+        staged = mode_name == "staged" and plans[0].staged_supported(S)
+        bf = plans[0].info["block_floats"]
+        recv = [torch.zeros(P * bf, dtype=torch.float32, device="cuda") for _ in range(P)]
+        send = [torch.zeros(P * bf, dtype=torch.float32, device="cuda") for _ in range(P)]
+        ptrs = [t.data_ptr() for t in recv]
+        d_img = torch.from_numpy(img).cuda()
+        stripes = [d_img[pl.info["row0"]:pl.info["row0"] + pl.info["valid_rows"]].contiguous() for pl in plans]
+        bufs = [pl.quirk_buffers() for pl in plans]
+        assert all(b is not None for b in bufs)
+        for r, pl in enumerate(plans):
+            pl.quirk_local(stripes[r] if pl.info["valid_rows"] > 0 else None)
+            if pl.info["valid_rows"] <= 0:
+                continue
+            if staged:
+                pl.row_pass_staged(stripes[r], ptrs, S)
+            elif mode_name == "push":
+                pl.row_pass_push(stripes[r], ptrs, 3)
+            elif mode_name == "plain":
+                pl.row_pass(stripes[r], send[r])
+            else:
+                pl.row_pass_peer(stripes[r], ptrs)
+        torch.cuda.synchronize()
+        # the all-reduce (SUM) of the two correction buffers over the ranks
+        tot_c = sum(b[0].clone() for b in bufs)
+        tot_i = sum(b[1].clone() for b in bufs)
+        for b in bufs:
+            b[0].copy_(tot_c)
+            b[1].copy_(tot_i)
+        if mode_name == "plain":                            # local send buffers + all-to-all by copies
+            chf = bf // 3
+            recv = [torch.cat([send[s].view(3, P, chf)[ch, r] for ch in range(3) for s in range(P)]) for r in range(P)]
+        outs = []
+        for r, pl in enumerate(plans):
+            pl.quirk_finish()
+            oc = torch.zeros((rows, 2 * pl.info["cpp"], 3), dtype=torch.uint8, device="cuda")
+            if staged:
+                for k in range(S):
+                    for q in plans:
+                        q.stage_wait(k)
+                    pl.col_pass_stage(recv[r], oc, k, S)
+            else:
+                pl.col_pass(recv[r], oc)
+            outs.append(oc)
+        torch.cuda.synchronize()
+        full = torch.cat(outs, 1)[:, :cols]
+        assert torch.equal(full, single), (rows, cols, sigma, P, mode_name, int((full.int() - single.int()).abs().max()))
+        for pl in plans + [p1]:
+            pl.close()
 
 
 @pytest.mark.gpu

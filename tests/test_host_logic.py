@@ -177,6 +177,10 @@ dist.init_process_group("gloo", init_method="tcp://127.0.0.1:%s" % os.environ["B
 rank, n = dist.get_rank(), dist.get_world_size()
 emu = Emulator()
 for rows, cols, sigma, mode in [(64, 96, 2.0, 0), (135, 241, 6.0, 1), (101, 75, 3.0, 0)]:
+    # pffft mode sharded: the CPU emulator has the full-length kernel's Nyquist handling only (the overlap-save
+    # corrections are CUDA kernels, covered by test_gauss_sharded_pffft_mode_emulated_on_one_gpu)
+    if mode == 1: os.environ["BLUR_B200_QUIRK_SHARDED"] = "full"
+    else: os.environ.pop("BLUR_B200_QUIRK_SHARDED", None)
     img = synth("noise", rows, cols, 9)
     def row_pass(stripe, q):
         assert emu.lib.emul_row_pass(stripe.data_ptr(), q.data_ptr(), rows, cols, sigma, mode, rank, n) == 0
@@ -194,6 +198,9 @@ for rows, cols, sigma, mode in [(64, 96, 2.0, 0), (135, 241, 6.0, 1), (101, 75, 
     assert np.array_equal(full, single), (rows, cols)
     ref = Oracle().gauss_blur_1d(img, sigma, mode)
     assert np.abs(full.astype(int) - ref.astype(int)).max() <= 1
+    # return exchange: column stripes -> the row stripes the input came in
+    back = sb.to_row_stripe()
+    assert back.shape == (g.valid_rows, cols, 3) and np.array_equal(back.numpy(), single[g.row0:g.row0 + g.valid_rows]), (rows, cols)
 dist.barrier()
 print("rank", rank, "ok")
 '''

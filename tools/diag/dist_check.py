@@ -28,6 +28,17 @@ for rows, cols, sigma in cases:
     ref = plan.run(full, torch.empty_like(full))
     mine = ref[:, g.col0:g.col0 + g.valid_cols]
     same = bool(torch.equal(mine, out_cols)) if g.valid_cols > 0 else True
+    # return exchange: back to the row stripes the input came in
+    back = sb.to_row_stripe()
+    same = same and bool(torch.equal(back, ref[g.row0:g.row0 + g.valid_rows]))
+    # pffft mode (Nyquist corrections summed over the ranks) against the single-GPU pffft-mode plan
+    if (rows, cols) != (16384, 16384) or "--headline" in sys.argv:
+        sbq = ShardedGaussBlur(rows, cols, sigma, bb.NYQUIST_PFFFT, device=dev)
+        planq = bb.GaussPlan(rows, cols, sigma, bb.NYQUIST_PFFFT, device=local)
+        refq = planq.run(full, torch.empty_like(full))
+        gotq = sbq.run(stripe)
+        same = same and (bool(torch.equal(refq[:, g.col0:g.col0 + g.valid_cols], gotq)) if g.valid_cols > 0 else True)
+        planq.close(); del sbq, refq
     # streamed host path: three different images through run_host_stream == run() on each
     imgs = [np.random.default_rng(70 + i).integers(0, 256, (rows, cols, 3), dtype=np.uint8) for i in range(3)]
     h_ins = [torch.from_numpy(im[g.row0:g.row0 + g.valid_rows].copy()).pin_memory() for im in imgs]
