@@ -154,7 +154,14 @@ def sweep(image: np.ndarray, flag: int) -> None:
         else:
             t0 = time.perf_counter()
             # Source.cpp:627-634 calls Test(image, flag, sqrt(x)) for every flag: FastBoxBlur gets ksize = int(nsmooth^2) ~ x
-            run_test(img, flag, sigma, quiet=True)
+            try:
+                run_test(img, flag, sigma, quiet=True)
+            except Exception as e:                      # noqa: BLE001  (a window wider than the kernels take: record it, go on)
+                line["error"] = str(e)
+                print(json.dumps(line), flush=True)
+                x += 225
+                y += 150
+                continue
             line["host_call_ms"] = (time.perf_counter() - t0) * 1e3
             if flag == 4:
                 k = 2 * ((int(sigma * sigma) - 1) // 2) + 1

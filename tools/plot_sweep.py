@@ -56,7 +56,7 @@ def main():
     ci = 0
     sizes = None
     for path in a.jsonl:
-        rows = load_jsonl(path)
+        rows = [r for r in load_jsonl(path) if "error" not in r]
         if not rows:
             continue
         nm = rows[0].get("name", os.path.basename(path))
