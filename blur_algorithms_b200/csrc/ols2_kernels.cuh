@@ -22,7 +22,10 @@
 
 namespace blurb200 {
 
-constexpr int kOls2RowWarps = 4;          // warps (independent workers) per row-pass CTA
+#ifndef BLUR_OLS2_ROW_WARPS
+#define BLUR_OLS2_ROW_WARPS 4
+#endif
+constexpr int kOls2RowWarps = BLUR_OLS2_ROW_WARPS;          // warps (independent workers) per row-pass CTA
 #ifndef BLUR_OLS2_ROW_CTAS
 #define BLUR_OLS2_ROW_CTAS 3
 #endif
