@@ -420,7 +420,12 @@ def main() -> None:
                 tc += e[1].elapsed_time(e[2])
             return tr / reps, tc / reps
 
-        if not multi:
+        direct = (not multi) and bool(plan.info.get("direct"))
+        if direct:
+            # narrow kernel: the whole blur is ONE fused direct-convolution kernel (csrc/direct_conv.cu); there are no passes to time
+            row_ms = colil_ms = None
+            pass_px = npx
+        elif not multi:
             q = torch.empty(plan.info["block_floats"], dtype=torch.float32, device=dev)
             oc = torch.empty((rows, 2 * plan.info["cpp"], 3), dtype=torch.uint8, device=dev)
             row_ms, colil_ms = time_passes(lambda: plan.row_pass(d_in, q), lambda: plan.col_pass(q, oc))
@@ -434,8 +439,12 @@ def main() -> None:
         kn = (("ols2_row_kernel" if two else "ols_row_kernel"),
               ("ols2_col_kernel" if plan.info["ols_L_col"] == 1024 else "ols_col_kernel") + " (+interleave_oct_kernel)") if algo == 1 else \
              ("fft_conv_kernel<RowIO>", "fft_conv_kernel<ColIO> (+interleave_u8_kernel)")
-        dom_name, dom_ms = (kn[0], row_ms) if row_ms >= colil_ms else (kn[1], colil_ms)
-        achieved = GAUSS_BYTES_PER_PX_PASS * pass_px / (dom_ms * 1e-3) / 1e9
+        if direct:
+            dom_name, dom_ms = "direct_gauss_kernel (row + column convolution fused, float32 intermediate in shared memory)", ms_per_step
+            achieved = GAUSS_BYTES_PER_PX_STEP * pass_px / (dom_ms * 1e-3) / 1e9      # the contract's 30 B/px for the whole blur
+        else:
+            dom_name, dom_ms = (kn[0], row_ms) if row_ms >= colil_ms else (kn[1], colil_ms)
+            achieved = GAUSS_BYTES_PER_PX_PASS * pass_px / (dom_ms * 1e-3) / 1e9
         traffic = None
         tp = os.path.join(ROOT, "profiles", "traffic.json")
         if os.path.exists(tp) and not multi:
@@ -448,8 +457,12 @@ def main() -> None:
         roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                     "traffic": traffic, "kernel": dom_name, "kernel_ms": dom_ms, "row_pass_ms": row_ms,
                     "col_pass_plus_interleave_ms": colil_ms, "peak_source": peak_src,
-                    "algorithmic_bytes_per_launch": GAUSS_BYTES_PER_PX_PASS * pass_px,
+                    "algorithmic_bytes_per_launch": (GAUSS_BYTES_PER_PX_STEP if direct else GAUSS_BYTES_PER_PX_PASS) * pass_px,
                     "step_achieved_GBps": step_gbps, "step_frac": step_gbps / peak}
+        if direct:
+            roofline["note"] = ("algorithmic bytes = SURVEY 8d's 30 B/px of the two-pass pipeline; the fused kernel itself moves only the "
+                                "compulsory 6 B/px (uint8 in + out) through HBM")
+            roofline["compulsory_bytes_per_launch"] = 6.0 * pass_px
 
         # ---- end to end through the host entry point (pinned host buffers, copies inside)
         e2e = None

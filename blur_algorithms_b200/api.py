@@ -145,6 +145,8 @@ class GaussPlan:
                 "launches_per_run", "threads_row", "threads_col", "batch_row", "batch_col", "smem_row", "smem_col",
                 "algo", "ols_L_row", "ols_L_col", "ols_V_row", "ols_V_col", "ols_nblocks_row", "ols_nblocks_col", "rqs"]
         self.info = {k: int(v) for k, v in zip(keys, info)}
+        # whole-image entries on the fused direct-convolution kernel (narrow kernels, single GPU)
+        self.info["direct"] = int(lib.blur_b200_gauss_plan_uses_direct(self._h))
 
     def close(self) -> None:
         if self._h:

@@ -18,6 +18,7 @@
 #include "fft_plan.hpp"
 #include "ols_launch.hpp"
 #include "ols_plan.hpp"
+#include "direct_conv.hpp"
 
 namespace blurb200 {
 __attribute__((visibility("hidden"))) void note_launches(uint64_t n);   // counter of this library's own kernel launches (other TUs)
@@ -573,6 +574,10 @@ struct blur_b200_plan {
     uint8_t* d_u = nullptr;           // [3][2*cpp][rows]
     int* d_cnt = nullptr;             // fused interleave of the two-factor column kernel: arrival counters per item
     bool col_fuse = false;            // BLUR_B200_COL_FUSE=1 at plan creation
+    // narrow kernels on one GPU: the whole-image entries (run_device, run_host*) use the fused direct-convolution
+    // kernel (direct_conv.cu) instead of the two FFT passes; the pass-wise entries keep the FFT kernels
+    bool direct = false;
+    float* d_dtaps = nullptr;         // [pad + 1] taps at offsets 0..pad
     // pffft Nyquist quirk served by the overlap-save kernels (single GPU): per-line corrections
     bool quirk_ols = false;
     double quirk_c_row = 0, quirk_c_col = 0;      // (K[0] - K[N/2]) / N of each axis
@@ -752,6 +757,19 @@ int plan_create_impl(blur_b200_plan* p, const GaussGeometry& gg, int rows, int c
     CU_TRY(cudaMemset(p->d_q, 0, sizeof(float) * p->block_floats * nranks));   // phantom column of an odd width stays 0
     CU_TRY(cudaMalloc(&p->d_u, static_cast<size_t>(3) * 2 * p->cpp * rows));
     if (const char* e = std::getenv("BLUR_B200_COL_FUSE")) p->col_fuse = std::atoi(e) != 0;
+    {
+        // direct path: measured faster than the block FFTs up to 41 taps (BLUR_B200_DIRECT=0 keeps the FFT kernels)
+        const char* e = std::getenv("BLUR_B200_DIRECT");
+        const bool want = !(e && std::atoi(e) == 0);
+        if (want && nranks == 1 && p->algo == 1 && gg.pad >= 1 && gg.pad <= kDirectMaxPad) {
+            std::vector<float> taps;
+            get_gaussian(taps, sigma, gg.ksize, gg.n_row);          // rotated: offset k at index k
+            taps.resize(static_cast<size_t>(gg.pad) + 1);
+            CU_TRY(cudaMalloc(&p->d_dtaps, sizeof(float) * taps.size()));
+            CU_TRY(cudaMemcpy(p->d_dtaps, taps.data(), sizeof(float) * taps.size(), cudaMemcpyHostToDevice));
+            p->direct = true;
+        }
+    }
     if (p->col_fuse && p->algo == 1 && p->ols_col.R2) {
         const size_t n = static_cast<size_t>(p->qpitch / 32 + 2) * p->ols_col.nblocks;
         CU_TRY(cudaMalloc(&p->d_cnt, sizeof(int) * n));
@@ -1027,7 +1045,7 @@ void blur_b200_gauss_plan_destroy(blur_b200_plan* p)
     cudaFree(p->d_ols_twa_row); cudaFree(p->d_ols_twa_col); cudaFree(p->d_ols_twb);
     cudaFree(p->d_ols_kt_row); cudaFree(p->d_ols_kt_col);
     cudaFree(p->d_ols2_tw); cudaFree(p->d_ols2_kt);
-    cudaFree(p->d_q); cudaFree(p->d_u); cudaFree(p->d_cnt); cudaFree(p->d_corr_row); cudaFree(p->d_corr_col); cudaFree(p->d_insum); cudaFree(p->d_taps);
+    cudaFree(p->d_q); cudaFree(p->d_u); cudaFree(p->d_cnt); cudaFree(p->d_dtaps); cudaFree(p->d_corr_row); cudaFree(p->d_corr_col); cudaFree(p->d_insum); cudaFree(p->d_taps);
     for (uint8_t* b : p->d_sin) cudaFree(b);
     for (uint8_t* b : p->d_sout) cudaFree(b);
     if (p->h2d_stream) cudaStreamDestroy(p->h2d_stream);
@@ -1069,11 +1087,40 @@ int blur_b200_gauss_plan_info(const blur_b200_plan* p, int64_t info[24])
     return BLUR_B200_OK;
 }
 
+// Whole blur through the fused direct-convolution kernel (plans with p->direct).  The kernel's tiles read their
+// neighbours' input pixels, so an in-place call goes through the plan's U buffer (at least one image large).
+static int run_direct(blur_b200_plan* p, const uint8_t* d_in, uint8_t* d_out, cudaStream_t st)
+{
+    DirectArgs a{};
+    a.in = d_in; a.rows = p->rows; a.cols = p->cols; a.pad = p->gg.pad; a.taps = p->d_dtaps;
+    if (p->quirk_ols) {
+        // pffft_ semantics: the same per-line Nyquist corrections the FFT epilogues add
+        quirk_rows_kernel<<<p->rows, 128, 0, st>>>(d_in, p->cols, p->gg.pad, p->quirk_c_row, p->d_corr_row, p->rows,
+                                                   p->cols % 4 == 0 && reinterpret_cast<uintptr_t>(d_in) % 4 == 0);
+        CU_TRY(cudaGetLastError());
+        ++g_launches;
+        const int rc = quirk_prepare_cols(p, d_in, st);
+        if (rc) return rc;
+        a.corr_row = p->d_corr_row; a.corr_row_pitch = p->rows;
+        a.corr_col = p->d_corr_col; a.corr_col_pitch = p->qpitch;
+    }
+    const size_t nbytes = static_cast<size_t>(p->rows) * p->cols * 3;
+    const bool alias = d_in == d_out || (d_out < d_in + nbytes && d_in < d_out + nbytes);
+    a.out = alias ? p->d_u : d_out;
+    CU_TRY(launch_direct_gauss(a, st));
+    ++g_launches;
+    if (alias) CU_TRY(cudaMemcpyAsync(d_out, p->d_u, nbytes, cudaMemcpyDeviceToDevice, st));
+    return BLUR_B200_OK;
+}
+
+int blur_b200_gauss_plan_uses_direct(const blur_b200_plan* p) { return p && p->direct ? 1 : 0; }
+
 int blur_b200_gauss_run_device(blur_b200_plan* p, const uint8_t* d_in, uint8_t* d_out, void* stream)
 {
     if (!p || !d_in || !d_out || p->nranks != 1) return BLUR_B200_EINVAL;
     CU_TRY(cudaSetDevice(p->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
+    if (p->direct) return run_direct(p, d_in, d_out, st);
     int rc = run_row_pass(p, d_in, p->d_q, st);
     if (rc) return rc;
     bool fused = false;
@@ -1124,6 +1171,20 @@ int blur_b200_gauss_run_host_batch(blur_b200_plan* p, const uint8_t* const* h_in
     for (int i = 0; i < n; ++i) {
         const int k = i & (nbuf - 1);
         if (i >= nbuf) CU_TRY(cudaStreamWaitEvent(p->h2d_stream, p->ev_rowdone[k], 0));     // row pass of image i-2 has read d_sin[k]
+        if (p->direct) {
+            // narrow kernel: one upload, the fused direct kernel, one download; images still overlap on the three streams
+            CU_TRY(cudaMemcpyAsync(p->d_sin[k], h_in[i], nbytes, cudaMemcpyHostToDevice, p->h2d_stream));
+            CU_TRY(cudaEventRecord(p->ev_h2d[0], p->h2d_stream));
+            CU_TRY(cudaStreamWaitEvent(sc, p->ev_h2d[0], 0));
+            if (i >= nbuf) CU_TRY(cudaStreamWaitEvent(sc, p->ev_d2hdone[k], 0));             // image i-2 has left d_sout[k]
+            const int rc = run_direct(p, p->d_sin[k], p->d_sout[k], sc);
+            if (rc) return rc;
+            CU_TRY(cudaEventRecord(p->ev_rowdone[k], sc));
+            CU_TRY(cudaStreamWaitEvent(p->d2h_stream, p->ev_rowdone[k], 0));
+            CU_TRY(cudaMemcpyAsync(h_out[i], p->d_sout[k], nbytes, cudaMemcpyDeviceToHost, p->d2h_stream));
+            CU_TRY(cudaEventRecord(p->ev_d2hdone[k], p->d2h_stream));
+            continue;
+        }
         for (int c = 0; c < nchunks; ++c) {
             const int p0 = std::min(npairs, static_cast<int>(static_cast<int64_t>(nwaves) * c / nchunks) * wave_pairs);
             const int p1 = c + 1 == nchunks ? npairs : std::min(npairs, static_cast<int>(static_cast<int64_t>(nwaves) * (c + 1) / nchunks) * wave_pairs);

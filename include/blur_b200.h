@@ -96,6 +96,11 @@ int blur_b200_gauss_shard_geometry(int rows, int cols, double sigma, int nyquist
 /* Whole blur, device resident: d_in and d_out are uint8 [rows][cols][3]; may alias (in place,
  * like image.data in the reference). */
 int blur_b200_gauss_run_device(blur_b200_plan *plan, const uint8_t *d_in, uint8_t *d_out, void *stream);
+/* 1 if the whole-image entries of this plan (run_device, run_host, run_host_batch, u8c3) use the fused
+ * direct-convolution kernel instead of the two FFT passes: single-GPU plans whose kernel half width is <= 20
+ * (sigma <= ~6.3; BASELINE config 1).  Same convolution (reflect-101, the float taps of getGaussian,
+ * Source.cpp:75-102), evaluated tap by tap in fp32; the pass-wise entries below always use the FFT kernels. */
+int blur_b200_gauss_plan_uses_direct(const blur_b200_plan *plan);
 
 /* Whole blur on host buffers (pinned or pageable); H2D + kernels + D2H.  In place allowed. */
 int blur_b200_gauss_run_host(blur_b200_plan *plan, const uint8_t *h_in, uint8_t *h_out);

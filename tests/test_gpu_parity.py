@@ -242,6 +242,7 @@ def test_gauss_errors(bb):
 def test_gauss_sharded_emulated_on_one_gpu(bb, torch, monkeypatch):
     """P ranks' plans executed one after another on one GPU with the all-to-all done by copies:
     bit-identical to the single-plan result (SURVEY.md §4 multi-GPU test plan)."""
+    monkeypatch.setenv("BLUR_B200_DIRECT", "0")       # narrow kernels: the single-GPU plan would take the direct kernel, the sharded ones cannot
     for rows, cols, sigma, mode, P in [(135, 241, 6.0, 1, 3), (240, 320, 5.0, 0, 2), (256, 256, 3.0, 0, 8)]:
         if mode == 1:
             monkeypatch.setenv("BLUR_B200_QUIRK_SHARDED", "full")      # round 1's sharded pffft path: the full-length kernel
@@ -652,6 +653,7 @@ def test_gauss_fused_interleave_variant_bit_identical(bb, torch, monkeypatch):
         d = torch.from_numpy(synth("noise", rows, cols, 8)).cuda()
         monkeypatch.delenv("BLUR_B200_COL_FUSE", raising=False)
         monkeypatch.setenv("BLUR_B200_OLS2", "1")
+        monkeypatch.setenv("BLUR_B200_DIRECT", "0")
         p0 = bb.GaussPlan(rows, cols, sigma, 0)
         a = p0.run(d, torch.empty_like(d))
         monkeypatch.setenv("BLUR_B200_COL_FUSE", "1")
@@ -661,6 +663,56 @@ def test_gauss_fused_interleave_variant_bit_identical(bb, torch, monkeypatch):
         torch.cuda.synchronize()
         assert torch.equal(a, b) and torch.equal(a, b2), (rows, cols, sigma)
         p0.close(); p1.close()
+
+
+@pytest.mark.gpu
+def test_gauss_direct_kernel_narrow_kernels(bb, oracle, torch, monkeypatch):
+    """Half widths up to 20 (sigma <= ~6.3, BASELINE config 1) run as one fused direct-convolution kernel on a single
+    GPU: +-1 LSB against the oracle in both Nyquist modes, against the FFT kernels, in place and out of place, at
+    ragged sizes and for every pad the kernel is instantiated for."""
+    for rows, cols, sigma in [(1080, 1920, 5.0), (270, 481, 5.0), (65, 130, 1.0), (200, 77, 2.2), (333, 1000, 6.2), (64, 64, 0.7)]:
+        img = synth("noise", rows, cols, 21)
+        for mode in (0, 1):
+            monkeypatch.delenv("BLUR_B200_DIRECT", raising=False)
+            p = bb.GaussPlan(rows, cols, sigma, mode)
+            assert p.info["direct"] == 1 and 1 <= p.info["pad"] <= 20, (sigma, p.info["pad"])
+            d = torch.from_numpy(img).cuda()
+            out = p.run(d, torch.empty_like(d)).cpu().numpy()
+            p.run(d)                                             # in place: through the plan's scratch image
+            assert np.array_equal(d.cpu().numpy(), out)
+            ref = oracle.gauss_blur_1d(img, sigma, mode)
+            assert lsb(out, ref) <= 1, (rows, cols, sigma, mode)
+            h = img.copy()
+            p.run_host(h)
+            assert np.array_equal(h, out)
+            p.close()
+            monkeypatch.setenv("BLUR_B200_DIRECT", "0")
+            pf = bb.GaussPlan(rows, cols, sigma, mode)
+            assert pf.info["direct"] == 0
+            d2 = torch.from_numpy(img).cuda()
+            fft = pf.run(d2).cpu().numpy()
+            dd = np.abs(fft.astype(int) - out.astype(int))
+            assert dd.max() <= 1 and (dd > 0).mean() < 1e-3, (rows, cols, sigma, mode, float((dd > 0).mean()))
+            pf.close()
+    monkeypatch.delenv("BLUR_B200_DIRECT", raising=False)
+    pads = set()
+    for s10 in range(4, 66):                                    # sigma 0.4 .. 6.5: every pad 1 .. 20
+        sigma = s10 / 10.0
+        p = bb.GaussPlan(96, 160, sigma, 0)
+        if p.info["direct"]:
+            pads.add(p.info["pad"])
+            img = synth("noise", 96, 160, s10)
+            d = torch.from_numpy(img).cuda()
+            assert lsb(p.run(d).cpu().numpy(), oracle.gauss_blur_1d(img, sigma, 0)) <= 1, sigma
+        p.close()
+    assert pads == set(range(1, 21)), sorted(pads)
+    imgs = [synth("noise", 300, 200, 30 + i) for i in range(5)]      # streamed host batch
+    p = bb.GaussPlan(300, 200, 4.0, 0)
+    outs = [np.empty_like(im) for im in imgs]
+    p.run_host_batch(imgs, outs)
+    for im, o in zip(imgs, outs):
+        assert lsb(o, oracle.gauss_blur_1d(im, 4.0, 0)) <= 1
+    p.close()
 
 
 # ---------------------------------------------------------------- FFT box blur (`#define boxblur`)

@@ -1,5 +1,6 @@
 """torchrun check: sharded blur over WORLD_SIZE GPUs is bit-identical to the single-GPU blur."""
 import os, sys
+os.environ.setdefault("BLUR_B200_DIRECT", "0")   # narrow kernels: single-GPU plans would take the direct kernel, sharded ones the FFTs
 import numpy as np
 import torch
 import torch.distributed as dist
