@@ -371,37 +371,6 @@ quirk_col_corr(const int* __restrict__ partial, int cols, int rows, int pad, con
     corr[static_cast<size_t>(ch) * qpitch + (x - xoff)] = static_cast<float>(c * acc);
 }
 
-// ------------------------------------------------------------------ exchange kernel
-// The distributed flip_block (Source.cpp:540) of the sharded plan: after a chunk of row pairs has
-// been transformed into the local send buffer, this kernel pushes the blocks owned by the other
-// GPUs into their receive buffers through NVLink peer mappings with 128-bit stores, while the row
-// pass of the next chunk runs on the compute stream.  One segment = rows [r0, r1) of one
-// (channel, destination) block: contiguous on both sides.
-struct PushArgs {
-    static constexpr int kMaxSeg = 3 * 7;
-    const float4* src[kMaxSeg];
-    float4* dst[kMaxSeg];
-    int nseg;
-    unsigned n4;                 // float4 per segment
-};
-
-__global__ void __launch_bounds__(256)
-q_push_kernel(const __grid_constant__ PushArgs a)
-{
-    const unsigned stride = gridDim.x * 256u;
-    for (int s = blockIdx.y; s < a.nseg; s += gridDim.y) {
-        const float4* __restrict__ src = a.src[s];
-        float4* __restrict__ dst = a.dst[s];
-        unsigned i = blockIdx.x * 256u + threadIdx.x;
-        for (; i + 3 * stride < a.n4; i += 4 * stride) {           // four loads in flight per thread
-            const float4 v0 = __ldcs(src + i), v1 = __ldcs(src + i + stride);
-            const float4 v2 = __ldcs(src + i + 2 * stride), v3 = __ldcs(src + i + 3 * stride);
-            dst[i] = v0; dst[i + stride] = v1; dst[i + 2 * stride] = v2; dst[i + 3 * stride] = v3;
-        }
-        for (; i < a.n4; i += stride) dst[i] = __ldcs(src + i);
-    }
-}
-
 // ------------------------------------------------------------------ box blur kernels
 // The fused one-kernel-per-pass path lives in boxblur.cu; the two kernels below are the general
 // fallback (any channel count, any window that fits a row in shared memory).
@@ -595,10 +564,8 @@ struct blur_b200_plan {
     float* d_q_recv = nullptr;        // unused on a single GPU
     int num_sms = 148;
     cudaStream_t stream = nullptr;
-    cudaStream_t push_stream = nullptr;            // exchange kernels of the sharded plan
     static constexpr int kMaxChunks = 16;
     cudaEvent_t ev_chunk[kMaxChunks] = {};
-    cudaEvent_t ev_pushed = nullptr;
     cudaStream_t ce_stream[7] = {};                // one per destination GPU: copies to different peers run on different engines
     cudaEvent_t ev_ce[7] = {};
     // staged exchange (blur_b200_gauss_row_pass_staged): row launch of stage k done / copy of stage k to destination d done
@@ -1055,9 +1022,7 @@ void blur_b200_gauss_plan_destroy(blur_b200_plan* p)
     for (cudaEvent_t e : p->ev_rowdone) if (e) cudaEventDestroy(e);
     for (cudaEvent_t e : p->ev_d2hdone) if (e) cudaEventDestroy(e);
     if (p->stream) cudaStreamDestroy(p->stream);
-    if (p->push_stream) cudaStreamDestroy(p->push_stream);
     for (cudaEvent_t e : p->ev_chunk) if (e) cudaEventDestroy(e);
-    if (p->ev_pushed) cudaEventDestroy(p->ev_pushed);
     for (cudaEvent_t e : p->ev_stage) if (e) cudaEventDestroy(e);
     for (auto& row : p->ev_scopy) for (cudaEvent_t e : row) if (e) cudaEventDestroy(e);
     for (cudaStream_t cs : p->ce_stream) if (cs) cudaStreamDestroy(cs);
@@ -1355,15 +1320,10 @@ int blur_b200_gauss_row_pass_push(blur_b200_plan* p, const uint8_t* d_in_stripe,
     CU_TRY(cudaSetDevice(p->device));
     cudaStream_t st = static_cast<cudaStream_t>(stream);
     const int N = p->nranks, rank = p->rank;
-    if (!p->push_stream) {
+    if (!p->ev_chunk[0]) {
         int prio_lo = 0, prio_hi = 0;
         CU_TRY(cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi));
-        CU_TRY(cudaStreamCreateWithPriority(&p->push_stream, cudaStreamNonBlocking, prio_hi));
-        // Same shared-memory carveout as the row kernel, or the two cannot share an SM: the copy
-        // CTAs must slip in beside the resident FFT CTAs of the next chunk.
-        CU_TRY(cudaFuncSetAttribute(q_push_kernel, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
         for (cudaEvent_t& e : p->ev_chunk) CU_TRY(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
-        CU_TRY(cudaEventCreateWithFlags(&p->ev_pushed, cudaEventDisableTiming));
         for (int d = 0; d + 1 < N; ++d) {
             if (!p->ce_stream[d]) CU_TRY(cudaStreamCreateWithPriority(&p->ce_stream[d], cudaStreamNonBlocking, prio_hi));
             CU_TRY(cudaEventCreateWithFlags(&p->ev_ce[d], cudaEventDisableTiming));
@@ -1406,42 +1366,22 @@ int blur_b200_gauss_row_pass_push(blur_b200_plan* p, const uint8_t* d_in_stripe,
         }
         if (N == 1 || diag == 2) continue;
         CU_TRY(cudaEventRecord(p->ev_chunk[c], st));
-        CU_TRY(cudaStreamWaitEvent(p->push_stream, p->ev_chunk[c], 0));
-        PushArgs a{};
-        a.n4 = static_cast<unsigned>(static_cast<size_t>(r1 - r0) * p->qpitch / 4);
-        for (int d = 1; d < N; ++d) {                       // start with the next rank: spread the NVSwitch ports
-            const int part = (rank + d) % N;
-            for (int ch = 0; ch < 3; ++ch) {
-                a.src[a.nseg] = reinterpret_cast<const float4*>(p->d_q + (static_cast<size_t>(ch) * N + part) * blk + static_cast<size_t>(r0) * p->qpitch);
-                a.dst[a.nseg] = reinterpret_cast<float4*>(q_peers[part] + (static_cast<size_t>(ch) * N + rank) * blk + static_cast<size_t>(r0) * p->qpitch);
-                ++a.nseg;
-            }
-        }
-        // Default: the GPU's copy engines move the segments (one contiguous peer copy each) — measured on
-        // B200 they run fully underneath the next chunk's FFT kernel at ~700 GB/s, while q_push_kernel
-        // (BLUR_B200_PUSH_ENGINE=sm) reaches the same rate alone but does not overlap the resident
-        // persistent row grid (profiles/r01_exchange_modes.txt).
-        static const int use_ce = !(std::getenv("BLUR_B200_PUSH_ENGINE") && !std::strcmp(std::getenv("BLUR_B200_PUSH_ENGINE"), "sm"));
-        if (use_ce) {
-            // segments are ordered destination-major, 3 channels each at a pitch of N blocks: one
-            // 2-D copy (3 rows) per destination and chunk
-            for (int d = 0; d + 1 < N; ++d) {
-                cudaStream_t cs = p->ce_stream[d];
-                CU_TRY(cudaStreamWaitEvent(cs, p->ev_chunk[c], 0));
-                CU_TRY(cudaMemcpy2DAsync(a.dst[3 * d], static_cast<size_t>(N) * blk * sizeof(float), a.src[3 * d],
-                                         static_cast<size_t>(N) * blk * sizeof(float), static_cast<size_t>(a.n4) * 16, 3,
-                                         cudaMemcpyDeviceToDevice, cs));
-            }
-        } else {
-            const int gx = std::max(1, std::min<int>(cdiv(static_cast<int>(a.n4), 256 * 4), std::max(1, 2 * p->num_sms / a.nseg)));
-            q_push_kernel<<<dim3(gx, a.nseg), 256, 0, p->push_stream>>>(a);
-            CU_TRY(cudaGetLastError());
-            ++g_launches;
+        // the GPU's copy engines move the finished chunk: per destination the three channel blocks sit at a pitch of
+        // N blocks on both sides, i.e. one 2-D peer copy (3 rows) per destination and chunk, each destination on its
+        // own stream.  (An SM copy kernel with 128-bit peer stores reached the same ~700 GB/s alone but did not get
+        // scheduled beside the resident persistent row grid — profiles/r01_exchange_modes.txt — and was removed.)
+        const size_t width = static_cast<size_t>(r1 - r0) * p->qpitch * sizeof(float);
+        const size_t pitch = static_cast<size_t>(N) * blk * sizeof(float);
+        for (int d = 0; d + 1 < N; ++d) {                   // start with the next rank: spread the NVSwitch ports
+            const int part = (rank + 1 + d) % N;
+            cudaStream_t cs = p->ce_stream[d];
+            CU_TRY(cudaStreamWaitEvent(cs, p->ev_chunk[c], 0));
+            CU_TRY(cudaMemcpy2DAsync(q_peers[part] + static_cast<size_t>(rank) * blk + static_cast<size_t>(r0) * p->qpitch, pitch,
+                                     p->d_q + static_cast<size_t>(part) * blk + static_cast<size_t>(r0) * p->qpitch, pitch, width, 3,
+                                     cudaMemcpyDeviceToDevice, cs));
         }
     }
     if (N > 1) {
-        CU_TRY(cudaEventRecord(p->ev_pushed, p->push_stream));
-        CU_TRY(cudaStreamWaitEvent(st, p->ev_pushed, 0));
         for (int d = 0; d + 1 < N; ++d) {
             CU_TRY(cudaEventRecord(p->ev_ce[d], p->ce_stream[d]));
             CU_TRY(cudaStreamWaitEvent(st, p->ev_ce[d], 0));

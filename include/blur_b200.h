@@ -141,12 +141,11 @@ int blur_b200_gauss_row_pass_peer(blur_b200_plan *plan, const uint8_t *d_in_stri
                                   void *stream);
 
 /* Row pass pipelined with the exchange (overlap-save plans, nranks <= 8): the stripe is cut into
- * `nchunks` groups of row pairs; each group is transformed into the plan's local send buffer (the
- * part this rank owns goes straight into q_peers[rank]) and, while the next group is being
- * transformed, a copy kernel on the plan's second stream pushes the finished group's blocks into the
- * owners' receive buffers q_peers[r] with 128-bit stores over the NVLink peer mappings.  On return
- * `stream` waits for every push.  Same caller-side synchronisation between ranks as
- * blur_b200_gauss_row_pass_peer. */
+ * `nchunks` wave-aligned groups of row pairs; each group is transformed into the plan's local send buffer (the
+ * part this rank owns goes straight into q_peers[rank]) and, while the next group is being transformed, the
+ * GPU's copy engines push the finished group's blocks into the owners' receive buffers q_peers[r] (one 2-D peer
+ * copy per destination and group over the NVLink peer mappings).  On return `stream` waits for every copy.
+ * Same caller-side synchronisation between ranks as blur_b200_gauss_row_pass_peer. */
 int blur_b200_gauss_row_pass_push(blur_b200_plan *plan, const uint8_t *d_in_stripe, float *const *q_peers, int npeers,
                                   int nchunks, void *stream);
 
