@@ -56,6 +56,10 @@ def _load() -> C.CDLL:
         "blur_b200_boxfft_klen": (i32, [i32, i32, f64]),
         "blur_b200_boxfft_plan_create": (i32, [C.POINTER(vp), i32, i32, f64, i32, i32]),
         "blur_b200_boxfft_u8c3": (i32, [vp, i32, i32, f64, i32]),
+        "blur_b200_gauss_halo_info": (i32, [vp, i32, i32, C.POINTER(C.c_int64)]),
+        "blur_b200_gauss_halo_row_pass": (i32, [vp, i32, i32, vp, vp, vp]),
+        "blur_b200_gauss_halo_push": (i32, [vp, i32, i32, vp, vp, vp, vp]),
+        "blur_b200_gauss_halo_col_pass": (i32, [vp, i32, i32, vp, vp, vp]),
         "blur_b200_gauss_quirk_buffers": (i32, [vp, C.POINTER(vp), C.POINTER(C.c_int64), C.POINTER(vp), C.POINTER(C.c_int64)]),
         "blur_b200_gauss_quirk_local": (i32, [vp, vp, vp]),
         "blur_b200_gauss_quirk_finish": (i32, [vp, vp]),
@@ -101,6 +105,7 @@ EXPORTED = [
     "blur_b200_gauss_plan_destroy", "blur_b200_gauss_plan_info", "blur_b200_gauss_plan_uses_direct", "blur_b200_gauss_run_device",
     "blur_b200_gauss_run_host", "blur_b200_gauss_run_host_batch", "blur_b200_gauss_u8c3", "blur_b200_release_cached", "blur_b200_gauss_row_pass",
     "blur_b200_gauss_col_pass", "blur_b200_gauss_row_pass_peer", "blur_b200_gauss_row_pass_push", "blur_b200_boxfft_klen", "blur_b200_boxfft_plan_create", "blur_b200_boxfft_u8c3",
+    "blur_b200_gauss_halo_info", "blur_b200_gauss_halo_row_pass", "blur_b200_gauss_halo_push", "blur_b200_gauss_halo_col_pass",
     "blur_b200_gauss_quirk_buffers", "blur_b200_gauss_quirk_local", "blur_b200_gauss_quirk_finish",
     "blur_b200_gauss_staged_supported",
     "blur_b200_gauss_row_pass_staged", "blur_b200_gauss_stage_wait", "blur_b200_gauss_col_pass_stage", "blur_b200_gauss_rowpass_f32", "blur_b200_fastboxblur_device",

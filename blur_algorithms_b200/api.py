@@ -207,6 +207,28 @@ class GaussPlan:
     def col_pass(self, d_q_chunks, d_out_cols, stream: int | None = None):
         check(lib.blur_b200_gauss_col_pass(self._h, _ptr(d_q_chunks), _ptr(d_out_cols), _stream() if stream is None else stream))
 
+    # row-stripe ("halo") sharding on a whole-image plan (blur_b200_gauss_halo_* in include/blur_b200.h)
+    def halo_info(self, rank: int, nranks: int):
+        """dict(row0, valid_rows, cap, halo, qpitch, q_floats, b0, nbl) of stripe `rank`, or None if the plan cannot
+        run row-stripe sharded (pffft mode, three-factor kernels)."""
+        o = (C.c_int64 * 8)()
+        if lib.blur_b200_gauss_halo_info(self._h, int(rank), int(nranks), o) != _lib.OK:
+            return None
+        return dict(zip(("row0", "valid_rows", "cap", "halo", "qpitch", "q_floats", "b0", "nbl"), (int(v) for v in o)))
+
+    def halo_row_pass(self, rank: int, nranks: int, d_in_stripe, d_q_local, stream: int | None = None):
+        check(lib.blur_b200_gauss_halo_row_pass(self._h, rank, nranks, _ptr(d_in_stripe) if d_in_stripe is not None else None,
+                                                _ptr(d_q_local), _stream() if stream is None else stream))
+
+    def halo_push(self, rank: int, nranks: int, d_q_local, q_up, q_down, stream: int | None = None):
+        """q_up / q_down: the neighbours' Q_local (tensor, int address or None at the image edges)"""
+        check(lib.blur_b200_gauss_halo_push(self._h, rank, nranks, _ptr(d_q_local), _ptr(q_up) if q_up is not None else None,
+                                            _ptr(q_down) if q_down is not None else None, _stream() if stream is None else stream))
+
+    def halo_col_pass(self, rank: int, nranks: int, d_q_local, d_out_rows, stream: int | None = None):
+        check(lib.blur_b200_gauss_halo_col_pass(self._h, rank, nranks, _ptr(d_q_local), _ptr(d_out_rows),
+                                                _stream() if stream is None else stream))
+
     # pffft-mode sharded plans (blur_b200_gauss_quirk_* in include/blur_b200.h)
     def quirk_buffers(self):
         """(corr_row, insum): zero-copy torch views of the plan's two correction buffers (float32 [3*rows],

@@ -1390,6 +1390,120 @@ int blur_b200_gauss_row_pass_push(blur_b200_plan* p, const uint8_t* d_in_stripe,
     return BLUR_B200_OK;
 }
 
+// ---- row-stripe ("halo") sharding ---------------------------------------------------------------------
+// The column pass is overlap-save too, so a rank that KEEPS its row stripe needs, besides its own row-pass
+// result, only `halo` rows of Q from the stripe above and below: 2 * halo * cols * 12 bytes per GPU instead
+// of rows * cols * 12 * (P - 1) / P^2 (65 MB instead of 352 MB at 16384^2, sigma = 50, P = 8), and the result
+// stays row-sharded like the input.  Stripes are whole column-pass blocks (V rows each) of the single-GPU
+// block grid, so every block is transformed with exactly the rows, tables and arithmetic of the single-GPU
+// plan: bit-identical output.  These entries work on an ordinary single-GPU plan of the WHOLE image (exact
+// mode, two-factor kernels); rank / nranks only select the stripe.  Q_local: float [3][cap + 2 halo][qpitch],
+// image row g of the stripe's band at local row g - row0 + halo.
+namespace {
+
+struct HaloGeom { int row0, valid_rows, cap, halo, b0, nbl, qrows; };
+
+bool halo_geom(const blur_b200_plan* p, int rank, int nranks, HaloGeom& g)
+{
+    if (!p || p->nranks != 1 || p->algo != 1 || p->quirk_ols || !p->ols_row.R2 || !p->ols_col.R2) return false;
+    if (nranks < 1 || rank < 0 || rank >= nranks) return false;
+    const int V = p->ols_col.V, nb = p->ols_col.nblocks;
+    const int bpr = cdiv(nb, nranks);
+    g.halo = p->ols_col.halo;
+    g.cap = bpr * V;
+    g.b0 = std::min(nb, rank * bpr);
+    g.nbl = std::max(0, std::min(nb, (rank + 1) * bpr) - g.b0);
+    g.row0 = std::min(p->rows, g.b0 * V);
+    g.valid_rows = std::max(0, std::min(p->rows, (g.b0 + g.nbl) * V) - g.row0);
+    g.qrows = g.cap + 2 * g.halo;
+    return true;
+}
+
+}  // namespace
+
+int blur_b200_gauss_halo_info(const blur_b200_plan* p, int rank, int nranks, int64_t out[8])
+{
+    HaloGeom g;
+    if (!out) return BLUR_B200_EINVAL;
+    if (!halo_geom(p, rank, nranks, g)) return p && p->nranks == 1 ? BLUR_B200_ESIZE : BLUR_B200_EINVAL;
+    out[0] = g.row0; out[1] = g.valid_rows; out[2] = g.cap; out[3] = g.halo; out[4] = p->qpitch;
+    out[5] = static_cast<int64_t>(3) * g.qrows * p->qpitch; out[6] = g.b0; out[7] = g.nbl;
+    return BLUR_B200_OK;
+}
+
+int blur_b200_gauss_halo_row_pass(blur_b200_plan* p, int rank, int nranks, const uint8_t* d_in_stripe, float* d_q_local, void* stream)
+{
+    HaloGeom g;
+    if (!halo_geom(p, rank, nranks, g) || !d_q_local) return BLUR_B200_EINVAL;
+    if (g.valid_rows <= 0) return BLUR_B200_OK;
+    if (!d_in_stripe) return BLUR_B200_EINVAL;
+    CU_TRY(cudaSetDevice(p->device));
+    OlsRowIO io{};
+    io.in = d_in_stripe; io.q = d_q_local + static_cast<size_t>(g.halo) * p->qpitch;
+    io.rows = g.valid_rows; io.cols = p->cols;
+    io.npairs = cdiv(g.valid_rows, 2);
+    io.srows = g.qrows; io.qpitch = p->qpitch; io.cpart = p->cpart; io.nparts = 1;     // channel planes are qrows rows apart
+    io.ax = p->ols_row;
+    io.nunits = io.ax.nblocks * io.npairs;
+    CU_TRY(launch_row_fft(p, io, p->num_sms, static_cast<cudaStream_t>(stream)));
+    ++g_launches;
+    return BLUR_B200_OK;
+}
+
+// this rank's first / last `halo` rows into the neighbours' bands (q_up = rank - 1's Q_local, q_down = rank + 1's;
+// nullptr at the image edges): two 2-D peer copies (three channel planes each) on the copy engines
+int blur_b200_gauss_halo_push(blur_b200_plan* p, int rank, int nranks, const float* d_q_local, float* q_up, float* q_down, void* stream)
+{
+    HaloGeom g;
+    if (!halo_geom(p, rank, nranks, g) || !d_q_local) return BLUR_B200_EINVAL;
+    if (g.valid_rows <= 0) return BLUR_B200_OK;
+    CU_TRY(cudaSetDevice(p->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const size_t qp = p->qpitch, plane = static_cast<size_t>(g.qrows) * qp * sizeof(float);
+    const int n = std::min(g.halo, g.valid_rows);
+    const size_t width = static_cast<size_t>(n) * qp * sizeof(float);
+    if (q_up && rank > 0)        // my rows [0, n) are rows [cap, cap + n) of the upper neighbour's stripe: its local rows halo + cap ...
+        CU_TRY(cudaMemcpy2DAsync(q_up + static_cast<size_t>(g.halo + g.cap) * qp, plane, d_q_local + static_cast<size_t>(g.halo) * qp, plane,
+                                 width, 3, cudaMemcpyDeviceToDevice, st));
+    if (q_down && rank + 1 < nranks && g.valid_rows == g.cap)    // my last n rows sit right above the lower neighbour's row 0: its local rows [halo - n, halo)
+        CU_TRY(cudaMemcpy2DAsync(q_down + static_cast<size_t>(g.halo - n) * qp, plane,
+                                 d_q_local + static_cast<size_t>(g.halo + g.valid_rows - n) * qp, plane, width, 3, cudaMemcpyDeviceToDevice, st));
+    return BLUR_B200_OK;
+}
+
+// column pass + interleave of this rank's blocks: d_out_rows uint8 [valid_rows][cols][3]
+int blur_b200_gauss_halo_col_pass(blur_b200_plan* p, int rank, int nranks, const float* d_q_local, uint8_t* d_out_rows, void* stream)
+{
+    HaloGeom g;
+    if (!halo_geom(p, rank, nranks, g) || !d_q_local || !d_out_rows) return BLUR_B200_EINVAL;
+    if (g.valid_rows <= 0) return BLUR_B200_OK;
+    CU_TRY(cudaSetDevice(p->device));
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int noct = std::min(p->qpitch / 8, cdiv(p->cols, 8));
+    OlsColIO io{};
+    io.rows = p->rows;                                  // image rows: block geometry, reflect patch, last block's valid count
+    io.noct = noct;
+    io.ax = p->ols_col;
+    io.b0 = g.b0; io.nbl = g.nbl;
+    io.nunits = ols2_col_npairs(io.noct, io.nbl);
+    // virtual bases: where image row 0 would be
+    io.u = p->d_u - static_cast<ptrdiff_t>(g.row0) * 8;
+    io.urows = g.cap;
+    io.qplane = static_cast<long long>(g.qrows) * p->qpitch;
+    io.qrow_lo = std::max(0, g.row0 - g.halo);
+    io.qrow_hi = std::min(p->rows, g.row0 + g.valid_rows + g.halo);
+    const float* q_virtual = d_q_local + (static_cast<ptrdiff_t>(g.halo) - g.row0) * static_cast<ptrdiff_t>(p->qpitch);
+    CU_TRY(launch_ols2_col(io, q_virtual, p->qpitch, g.qrows, p->d_ols2_tw, p->d_ols2_kt, p->num_sms, st));
+    ++g_launches;
+    const int vec = (static_cast<size_t>(p->cols) * 3 % 16 == 0) && (reinterpret_cast<uintptr_t>(d_out_rows) % 16 == 0) &&
+                    (reinterpret_cast<uintptr_t>(p->d_u) % 32 == 0) && (g.cap % 2 == 0);     // 16-byte loads of 4 rows: even plane height
+    dim3 grid(cdiv(cdiv(noct, 2), 32), cdiv(cdiv(g.valid_rows, 4), 8));
+    interleave_oct_kernel<<<grid, dim3(32, 8), 0, st>>>(p->d_u, d_out_rows, g.cap, noct, std::min(p->cols, noct * 8), p->cols, vec, 0, g.valid_rows);
+    CU_TRY(cudaGetLastError());
+    ++g_launches;
+    return BLUR_B200_OK;
+}
+
 // ---- pffft Nyquist quirk of a SHARDED overlap-save plan (Source.cpp:414-427) --------------------------
 // Row corrections are local to a stripe; the column corrections need sums over ALL rows: the integer column sums of
 // the input (d_insum partials) and the row corrections themselves (d_corr_row).  Sequence per blur on every rank:

@@ -290,8 +290,8 @@ BLUR_HD OlsColIO::Ctx ols2_col_ctx(const OlsColIO& io, int strip, int b, int m)
     c.valid = c.oct < io.noct;
     if (!c.valid) c.oct = io.noct - 1;
     const int blk = io.b0 + b;
-    c.ua = io.u + (static_cast<size_t>(c.ch) * io.noct + c.oct) * io.rows * 8;
-    c.qa = io.q + static_cast<size_t>(c.ch) * io.rows_total * io.qpitch + c.oct * 8;
+    c.ua = io.u + (static_cast<size_t>(c.ch) * io.noct + c.oct) * (io.urows ? io.urows : io.rows) * 8;
+    c.qa = io.q + static_cast<size_t>(c.ch) * (io.qplane ? static_cast<size_t>(io.qplane) : static_cast<size_t>(io.rows_total) * io.qpitch) + c.oct * 8;
     c.s = blk * io.ax.V - io.ax.halo;
     c.nvalid = io.rows - blk * io.ax.V < io.ax.V ? io.rows - blk * io.ax.V : io.ax.V;
     c.interior = c.s >= 0 && c.s + io.ax.L <= io.rows;

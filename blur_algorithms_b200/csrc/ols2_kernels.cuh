@@ -274,8 +274,9 @@ __device__ __forceinline__ void ols2_col_fetch(const OlsColIO& io, const OlsColI
 #pragma unroll
         for (int j = 0; j < kOls2R1; ++j) {
             const int r = r0 + R2 * j;
-            const bool ok = r >= 0 && r < io.rows_total;
-            cp_async16_zfill(base + 4 * (R2 + 1) * j, ok ? p + j * step : io.q, ok);
+            const bool ok = io.qrow_hi ? (r >= io.qrow_lo && r < io.qrow_hi) : (r >= 0 && r < io.rows_total);
+            // (a zero-filling copy still needs a mapped source address: the first row Q really holds)
+            cp_async16_zfill(base + 4 * (R2 + 1) * j, ok ? p + j * step : io.q + static_cast<size_t>(io.qrow_hi ? io.qrow_lo : 0) * io.qpitch, ok);
         }
     }
 }

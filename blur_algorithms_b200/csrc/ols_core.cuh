@@ -441,6 +441,12 @@ struct OlsColIO {
     uint8_t* out;
     int out_cols, ncols;
     int* cnt;              // one zero-initialised counter per item; the last arriver resets it
+    // Row-stripe ("halo") plans of the two-factor kernel: Q and U hold only a band of image rows.  q / u are then
+    // VIRTUAL bases (the address image row 0 would have), the channel planes are qplane floats / urows rows apart,
+    // and only rows [qrow_lo, qrow_hi) exist in Q (outside: the reflect-101 patch or zeros, as at the image edge).
+    // All four default (0) to the whole-image layout: qplane = rows_total * qpitch, urows = rows, [0, rows_total).
+    long long qplane;
+    int urows, qrow_lo, qrow_hi;
 
     struct Ctx {
         uint8_t* ua;       // U byte of (ch, oct, row 0, 0)

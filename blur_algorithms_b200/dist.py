@@ -406,3 +406,45 @@ class ShardedGaussBlur:
                 ev_dn.record(self._s_dn)
         self._s_dn.synchronize()
         cur.synchronize()
+
+
+class HaloShardedGaussBlur:
+    """Row-stripe ("halo") sharding of one image: input AND output row-sharded (SURVEY.md 8e's halo alternative,
+    reported beside the contract configuration, not instead of it).  Every rank keeps a stripe of whole column-pass
+    blocks, runs the row pass on it, pushes its first / last `halo` rows of the float32 intermediate into the two
+    neighbours' buffers (symmetric memory over NVLink, two copy-engine copies) and runs the column pass on its own
+    blocks: 2 * halo * cols * 12 bytes per GPU on the wire instead of rows * cols * 12 * (P - 1) / P^2, no all-to-all,
+    result bit-identical to the single-GPU plan.  Exact mode, kernels narrow enough for the two-factor blocks."""
+
+    def __init__(self, rows: int, cols: int, sigma: float, group=None, device: torch.device | None = None):
+        from .api import GaussPlan
+        self.group = group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.nranks = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+        self.plan = GaussPlan(rows, cols, sigma, 0, device=self.device.index or 0)
+        info = self.plan.halo_info(self.rank, self.nranks)
+        if info is None:
+            raise ValueError("this geometry cannot run row-stripe sharded (needs the two-factor kernels on both axes)")
+        self.info, self.rows, self.cols = info, rows, cols
+        self.row0, self.valid_rows = info["row0"], info["valid_rows"]
+        import torch.distributed._symmetric_memory as symm_mem
+        self.q_local = symm_mem.empty(info["q_floats"], dtype=torch.float32, device=self.device)
+        self.q_local.zero_()
+        self.symm = symm_mem.rendezvous(self.q_local, group if group is not None else dist.group.WORLD) if self.nranks > 1 else None
+        ptrs = [int(p) for p in self.symm.buffer_ptrs] if self.symm is not None else [self.q_local.data_ptr()]
+        self.q_up = ptrs[self.rank - 1] if self.rank > 0 else None
+        self.q_down = ptrs[self.rank + 1] if self.rank + 1 < self.nranks else None
+        self.out_rows = torch.zeros((max(self.valid_rows, 1), cols, 3), dtype=torch.uint8, device=self.device)
+
+    def run(self, in_stripe: torch.Tensor) -> torch.Tensor:
+        """in_stripe: uint8 [valid_rows, cols, 3] = image rows [row0, row0 + valid_rows).  Returns the same rows blurred."""
+        r, n, p = self.rank, self.nranks, self.plan
+        if self.symm is not None:
+            self.symm.barrier(channel=0)                 # the neighbours' column passes of the previous blur have read my halos
+        p.halo_row_pass(r, n, in_stripe if self.valid_rows > 0 else None, self.q_local)
+        p.halo_push(r, n, self.q_local, self.q_up, self.q_down)
+        if self.symm is not None:
+            self.symm.barrier(channel=1)                 # both neighbours' halos have landed here
+        p.halo_col_pass(r, n, self.q_local, self.out_rows)
+        return self.out_rows[: self.valid_rows]

@@ -149,6 +149,22 @@ int blur_b200_gauss_row_pass_peer(blur_b200_plan *plan, const uint8_t *d_in_stri
 int blur_b200_gauss_row_pass_push(blur_b200_plan *plan, const uint8_t *d_in_stripe, float *const *q_peers, int npeers,
                                   int nchunks, void *stream);
 
+/* Row-stripe ("halo") sharding of one image: every rank keeps a stripe of whole column-pass blocks, runs the row
+ * pass on it, receives only `halo` rows of the float32 intermediate from the stripe above and below, and runs the
+ * column pass on its own blocks: input AND output row-sharded, 2*halo*cols*12 bytes exchanged per GPU (65 MB
+ * instead of 352 MB at 16384^2 sigma=50 on 8 GPUs), output bit-identical to the single-GPU plan.  The entries take
+ * an ordinary single-GPU plan of the WHOLE image (exact mode, two-factor kernels: BLUR_B200_ESIZE otherwise);
+ * rank / nranks select the stripe.  info = {row0, valid_rows, stripe capacity, halo, qpitch, floats of Q_local,
+ * first block, blocks}.  Q_local (caller's, peer-mapped for the neighbours): float [3][capacity + 2*halo][qpitch].
+ * Sequence: halo_row_pass -> halo_push (q_up / q_down = the neighbours' Q_local, NULL at the image edges) ->
+ * cross-rank barrier -> halo_col_pass (d_out_rows: uint8 [valid_rows][cols][3]).  The halo variant of the
+ * distributed flip_block (Source.cpp:540); the contract configuration (row stripes -> all-to-all -> column
+ * stripes) is the sharded plan above. */
+int blur_b200_gauss_halo_info(const blur_b200_plan *plan, int rank, int nranks, int64_t info[8]);
+int blur_b200_gauss_halo_row_pass(blur_b200_plan *plan, int rank, int nranks, const uint8_t *d_in_stripe, float *d_q_local, void *stream);
+int blur_b200_gauss_halo_push(blur_b200_plan *plan, int rank, int nranks, const float *d_q_local, float *q_up, float *q_down, void *stream);
+int blur_b200_gauss_halo_col_pass(blur_b200_plan *plan, int rank, int nranks, const float *d_q_local, uint8_t *d_out_rows, void *stream);
+
 /* pffft-mode (BLUR_B200_NYQUIST_PFFFT) SHARDED overlap-save plans: the Nyquist quirk of Source.cpp:414-427 is a
  * per-line correction; a stripe's row corrections are local, the column corrections need two small sums over all
  * rows.  Per blur on every rank: blur_b200_gauss_quirk_local(stripe) -> row pass (any exchange entry above) ->

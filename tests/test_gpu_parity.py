@@ -646,6 +646,38 @@ def test_gauss_sharded_pffft_mode_emulated_on_one_gpu(bb, torch, mode_name):
 
 
 @pytest.mark.gpu
+def test_gauss_halo_sharding_emulated_on_one_gpu(bb, torch, monkeypatch):
+    """Row-stripe (halo) sharding, all ranks emulated on one GPU with the halo pushes as same-device copies: stripes of
+    whole column blocks, 2 * halo rows exchanged, output row-sharded and bit-identical to the single-GPU plan —
+    including a short last stripe, empty trailing ranks and image-edge blocks."""
+    monkeypatch.setenv("BLUR_B200_DIRECT", "0")
+    for rows, cols, sigma, P in [(4096, 1024, 50.0, 4), (3000, 777, 25.0, 2), (2200, 640, 30.0, 8), (1500, 1000, 9.0, 3), (5300, 512, 50.0, 8)]:
+        img = synth("noise", rows, cols, 13)
+        d_img = torch.from_numpy(img).cuda()
+        plan = bb.GaussPlan(rows, cols, sigma, 0)
+        want = plan.run(d_img, torch.empty_like(d_img))
+        infos = [plan.halo_info(r, P) for r in range(P)]
+        assert all(i is not None for i in infos), (rows, cols, sigma)
+        assert sum(i["valid_rows"] for i in infos) == rows and infos[0]["row0"] == 0
+        qs = [torch.zeros(i["q_floats"], dtype=torch.float32, device="cuda") for i in infos]
+        for r, i in enumerate(infos):
+            stripe = d_img[i["row0"]:i["row0"] + i["valid_rows"]].contiguous() if i["valid_rows"] > 0 else None
+            plan.halo_row_pass(r, P, stripe, qs[r])
+        for r in range(P):
+            plan.halo_push(r, P, qs[r], qs[r - 1] if r > 0 else None, qs[r + 1] if r + 1 < P else None)
+        outs = []
+        for r, i in enumerate(infos):
+            o = torch.zeros((max(i["valid_rows"], 1), cols, 3), dtype=torch.uint8, device="cuda")
+            plan.halo_col_pass(r, P, qs[r], o)
+            torch.cuda.synchronize()
+            outs.append(o[: i["valid_rows"]].clone())       # the plan's U scratch is shared by the emulated ranks
+        got = torch.cat(outs, 0)
+        assert torch.equal(got, want), (rows, cols, sigma, P, int((got.int() - want.int()).abs().max()))
+        plan.close()
+    assert bb.GaussPlan(600, 800, 5.0, 1).halo_info(0, 2) is None      # pffft mode: not offered
+
+
+@pytest.mark.gpu
 def test_gauss_fused_interleave_variant_bit_identical(bb, torch, monkeypatch):
     """BLUR_B200_COL_FUSE=1: the column kernel's last-arriver interleave (measured slower than the separate pass,
     kept as a knob) writes exactly the bytes of column pass + interleave_oct_kernel, ragged sizes included."""
