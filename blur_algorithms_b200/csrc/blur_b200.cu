@@ -1397,7 +1397,7 @@ int blur_b200_gauss_row_pass_push(blur_b200_plan* p, const uint8_t* d_in_stripe,
 // stays row-sharded like the input.  Stripes are whole column-pass blocks (V rows each) of the single-GPU
 // block grid, so every block is transformed with exactly the rows, tables and arithmetic of the single-GPU
 // plan: bit-identical output.  These entries work on an ordinary single-GPU plan of the WHOLE image (exact
-// mode, two-factor kernels); rank / nranks only select the stripe.  Q_local: float [3][cap + 2 halo][qpitch],
+// mode, two-factor column kernel); rank / nranks only select the stripe.  Q_local: float [3][cap + 2 halo][qpitch],
 // image row g of the stripe's band at local row g - row0 + halo.
 namespace {
 
@@ -1405,7 +1405,7 @@ struct HaloGeom { int row0, valid_rows, cap, halo, b0, nbl, qrows; };
 
 bool halo_geom(const blur_b200_plan* p, int rank, int nranks, HaloGeom& g)
 {
-    if (!p || p->nranks != 1 || p->algo != 1 || p->quirk_ols || !p->ols_row.R2 || !p->ols_col.R2) return false;
+    if (!p || p->nranks != 1 || p->algo != 1 || p->quirk_ols || !p->ols_col.R2) return false;     // banded Q/U: two-factor column kernel
     if (nranks < 1 || rank < 0 || rank >= nranks) return false;
     const int V = p->ols_col.V, nb = p->ols_col.nblocks;
     const int bpr = cdiv(nb, nranks);
