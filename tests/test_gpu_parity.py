@@ -160,7 +160,7 @@ def test_gauss_float32_intermediate_c2_c3(bb, oracle, torch, rows, cols, sigma, 
 def test_gauss_sharded_multi_gpu_bit_identity():
     """With >= 2 visible GPUs: torchrun tools/diag/dist_check.py on 2 (and 8 if present) GPUs — the
     sharded 16384 x 16384 sigma = 50 result (row stripes -> exchange -> column stripes) is bit-identical
-    to the single-GPU plan's on every rank."""
+    to the single-GPU plan's on every rank (incl. pffft mode and the return exchange); then tools/diag/halo_check.py."""
     import subprocess
     import sys
     import torch as t
@@ -174,6 +174,11 @@ def test_gauss_sharded_multi_gpu_bit_identity():
         r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
         assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
         assert "16384x16384" in r.stdout and "identical=True" in r.stdout
+        # row-stripe (halo) sharding beside it: input and output row-sharded, bit-identical as well
+        cmd = cmd[:-2] + [os.path.join(root, "tools", "diag", "halo_check.py")]
+        cmd[cmd.index("--master-port") + 1] = str(29750 + world)
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+        assert r.returncode == 0 and '"identical": true' in r.stdout, r.stdout[-2000:] + r.stderr[-2000:]
 
 
 def test_gauss_float32_intermediate(bb, oracle, torch):
