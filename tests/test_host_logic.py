@@ -293,3 +293,20 @@ def test_cli_ppm_roundtrip(tmp_path):
     assert open(p, "rb").read(2) == b"P6"
     assert np.array_equal(cli.read_image(p), img)
     assert cli.resize(img, 14, 10).shape == (14, 10, 3)
+
+
+def test_sweep_plot_tool(tmp_path):
+    """tools/plot_sweep.py (the equivalent of the reference's py/bench.png) renders the committed sweep
+    lines into a well-formed SVG with one device and one host series per file (+ the reference's four published
+    series when /root/reference is mounted)."""
+    import xml.dom.minidom
+    out = tmp_path / "sweep.svg"
+    files = [os.path.join(ROOT, "profiles", f"r02z_sweep_flag{f}.jsonl") for f in (3, 5)]
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "plot_sweep.py"), "--out", str(out)] + files,
+                       capture_output=True, text=True, timeout=120)
+    assert r.returncode == 0, r.stderr
+    doc = xml.dom.minidom.parse(str(out))
+    paths = doc.getElementsByTagName("path")
+    assert len(paths) >= 4
+    text = out.read_text()
+    assert "B200 pffft_ device-resident" in text and "B200 pocketfft_1D host call" in text
