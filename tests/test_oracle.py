@@ -246,6 +246,16 @@ def test_boxblur_build_tent_kernel_and_reference(oracle):
         im = synth("noise", rows, cols, 3)
         for flag, mode in ((5, 0), (3, 1)):
             assert np.array_equal(ref.test(im, flag, ns), oracle.boxfft_blur(im, ns, mode)), (rows, cols, ns, flag)
+        # pocketfft_2D's boxblur branches (Source.cpp:152-156,207-211,224-228); the restatement refuses windows that
+        # nearly fill the shorter side, where the reference's Reflect_101 clamps its pads (Utils.hpp:217-220)
+        if 2 * ns * ns > min(rows, cols):
+            continue
+        oracle.lib.orc_set_boxblur(1)
+        try:
+            two_d = oracle.gauss_blur_2d(im, ns)
+        finally:
+            oracle.lib.orc_set_boxblur(0)
+        assert np.array_equal(ref.test(im, 2, ns), two_d), (rows, cols, ns)
 
 
 def test_pffft_quirk_is_rank_one_correction(oracle):
