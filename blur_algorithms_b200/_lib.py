@@ -12,7 +12,8 @@ import os
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("BLUR_B200_LIB") or os.path.join(_HERE, "libblur_b200.so")   # env: experiment builds only
 
-OK, EINVAL, EPAD, ESIZE, ECUDA, ENOMEM = 0, 1, 2, 3, 4, 5
+OK, EINVAL, EPAD, ESIZE, ECUDA, ENOMEM, ESCRATCH = 0, 1, 2, 3, 4, 5, 6
+NOALLOC_SCRATCH_BYTES = 32 << 20   # BLUR_B200_NOALLOC_SCRATCH_BYTES of include/blur_b200.h
 NYQUIST_EXACT, NYQUIST_PFFFT = 0, 1
 
 
@@ -69,6 +70,7 @@ def _load() -> C.CDLL:
         "blur_b200_gauss_col_pass_stage": (i32, [vp, vp, vp, i32, i32, i32, vp]),
         "blur_b200_gauss_rowpass_f32": (i32, [vp, vp, vp, vp]),
         "blur_b200_fastboxblur_device": (i32, [vp, i32, i32, i32, i32, i32, i32, vp, vp]),
+        "blur_b200_fastboxblur_device_noalloc": (i32, [vp, i32, i32, i32, i32, i32, i32, vp]),
         "blur_b200_fastboxblur": (i32, [vp, i32, i32, i32, i32, i32]),
         "blur_b200_fastboxblur_batch_host": (i32, [vp, i32, i32, i32, i32, i32, i32]),
         "blur_b200_reflect_101_u8": (i32, [vp, vp, i32, i32, i32, i32, pi32, i32, vp]),
@@ -109,7 +111,7 @@ EXPORTED = [
     "blur_b200_gauss_quirk_buffers", "blur_b200_gauss_quirk_local", "blur_b200_gauss_quirk_finish",
     "blur_b200_gauss_staged_supported",
     "blur_b200_gauss_row_pass_staged", "blur_b200_gauss_stage_wait", "blur_b200_gauss_col_pass_stage", "blur_b200_gauss_rowpass_f32", "blur_b200_fastboxblur_device",
-    "blur_b200_fastboxblur", "blur_b200_fastboxblur_batch_host", "blur_b200_reflect_101_u8", "blur_b200_reflect_101_u8_host",
+    "blur_b200_fastboxblur_device_noalloc", "blur_b200_fastboxblur", "blur_b200_fastboxblur_batch_host", "blur_b200_reflect_101_u8", "blur_b200_reflect_101_u8_host",
     "blur_b200_deinterleave_u8_f32", "blur_b200_interleave_f32_u8", "blur_b200_flip_block_f32",
     "blur_b200_deinterleave_u8_f32_host", "blur_b200_interleave_f32_u8_host", "blur_b200_flip_block_f32_host",
     "blur_b200_deinterleave_typed", "blur_b200_interleave_typed", "blur_b200_flip_block_pixels",

@@ -21,7 +21,7 @@ from ._lib import NYQUIST_EXACT, NYQUIST_PFFFT, BlurB200Error, check, lib
 __all__ = [
     "isValidSize", "nearestTransformSize", "gaussian_window", "getGaussian", "gauss_geometry",
     "pffft_", "pocketfft_1D", "pocketfft_2D", "boxfft_blur", "boxfft_klen", "fastboxblur", "Reflect_101", "deinterleave_BGR",
-    "interleave_BGR", "flip_block", "dft_image", "Test", "GaussPlan", "fastboxblur_device", "fastboxblur_batch",
+    "interleave_BGR", "flip_block", "dft_image", "Test", "GaussPlan", "fastboxblur_device", "fastboxblur_device_noalloc", "fastboxblur_batch",
     "kernel_launches", "BlurB200Error", "NYQUIST_EXACT", "NYQUIST_PFFFT",
 ]
 
@@ -300,6 +300,17 @@ def fastboxblur_device(d_img, w: int, h: int, channels: int, ksize: int, passes:
     """Device-resident, batched variant: d_img is `batch` images back to back."""
     check(lib.blur_b200_fastboxblur_device(_ptr(d_img), w, h, channels, int(ksize), int(passes), batch,
                                            _ptr(d_scratch), _stream() if stream is None else stream))
+
+
+def fastboxblur_device_noalloc(d_img, w: int, h: int, channels: int, ksize: int, passes: int, batch: int,
+                               stream: int | None = None) -> None:
+    """fastboxblur_device without the scratch argument, for callers that may not allocate GPU memory (a node
+    inside another application's memory pool, a real-time loop): the second buffer is a fixed 32 MiB array
+    inside the library, shared by all calls on a GPU.  Raises BlurB200Error(ESCRATCH) when
+    w*h*channels*batch exceeds it.  Do not let two such calls overlap on one GPU; make the first call on each
+    GPU at set-up time.  Results equal fastboxblur_device byte for byte."""
+    check(lib.blur_b200_fastboxblur_device_noalloc(_ptr(d_img), w, h, channels, int(ksize), int(passes), batch,
+                                                   _stream() if stream is None else stream))
 
 
 # ---- layout utilities ---------------------------------------------------------------------------

@@ -952,6 +952,7 @@ const char* blur_b200_strerror(int code)
     case BLUR_B200_ESIZE: return "FFT length not plannable on one SM (valid sizes up to 28160)";
     case BLUR_B200_ECUDA: return "CUDA error";
     case BLUR_B200_ENOMEM: return "out of memory";
+    case BLUR_B200_ESCRATCH: return "image batch exceeds the built-in no-allocation work buffer (BLUR_B200_NOALLOC_SCRATCH_BYTES = 32 MiB)";
     default: return "unknown error";
     }
 }

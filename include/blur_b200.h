@@ -27,7 +27,9 @@ enum {
                                   read out of bounds (README.md:33-38); we refuse instead */
     BLUR_B200_ESIZE = 3,       /* FFT length not plannable / exceeds shared memory (N > 28160) */
     BLUR_B200_ECUDA = 4,       /* CUDA runtime error (see blur_b200_last_cuda_error) */
-    BLUR_B200_ENOMEM = 5
+    BLUR_B200_ENOMEM = 5,
+    BLUR_B200_ESCRATCH = 6     /* blur_b200_fastboxblur_device_noalloc only: the image batch is larger than
+                                  the library's built-in work buffer (BLUR_B200_NOALLOC_SCRATCH_BYTES) */
 };
 
 /* nyquist_mode for the Gaussian paths */
@@ -220,6 +222,23 @@ int blur_b200_fastboxblur(uint8_t *h_img, int w, int h, int channels, int ksize,
 /* `batch` contiguous host images (the C5 workload; the reference calls fastboxblur once per image,
  * Source.cpp:587), streamed in groups: uploads, kernels and downloads overlap.  In place. */
 int blur_b200_fastboxblur_batch_host(uint8_t *h_imgs, int w, int h, int channels, int ksize, int passes, int batch);
+
+/* FastBoxBlur for callers that cannot allocate GPU memory (no counterpart in the reference, whose fastboxblur
+ * works on host memory; added for this library's users).  Same arguments and byte-identical results as
+ * blur_b200_fastboxblur_device, minus d_scratch: the second buffer is a fixed array of
+ * BLUR_B200_NOALLOC_SCRATCH_BYTES that is part of the library's device image, so the call itself never
+ * allocates or frees anything.  Meant for plug-in nodes that only get their input/output surfaces from a
+ * host application's memory pool, and for real-time loops where cudaMalloc is off limits once running.
+ *   - w*h*channels*batch must not exceed BLUR_B200_NOALLOC_SCRATCH_BYTES: BLUR_B200_ESCRATCH otherwise.
+ *   - Runs on the calling thread's current GPU (d_img must live there).  The first call on each GPU resolves
+ *     the array's address and may load the kernels: make it at set-up, before any stream capture begins.
+ *   - One array per GPU, shared by every call: calls that can overlap on the GPU (different streams or
+ *     threads) corrupt each other — issue them one after another.  Old contents are harmless; every pass
+ *     writes its whole destination first, so nothing is zeroed between calls.
+ *   - Each GPU that runs any kernel of this library holds the 32 MiB until the process exits. */
+#define BLUR_B200_NOALLOC_SCRATCH_BYTES (32u << 20)
+int blur_b200_fastboxblur_device_noalloc(uint8_t *d_img, int w, int h, int channels, int ksize, int passes,
+                                         int batch, void *stream);
 
 /* ---- layout utilities (device pointers) ------------------------------------------------------ */
 /* Reflect_101<uint8_t,C>, Utils.hpp:212-243.  original_size = {rows, cols}.  Pads are clamped to
