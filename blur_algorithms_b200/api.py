@@ -339,16 +339,29 @@ _TYPE_CODES = {"torch.uint8": 0, "torch.uint16": 1, "torch.int32": 2, "torch.flo
 
 
 def _type_code(t) -> int:
+    """Element type code of a tensor / array, or of the first of a list or tuple of planes."""
+    if isinstance(t, (list, tuple)) and len(t):
+        t = t[0]
     try:
         return _TYPE_CODES[str(t.dtype)]
-    except KeyError:
-        raise BlurB200Error(_lib.EINVAL, f"element type {t.dtype} is not one of uint8 / uint16 / int32 / float32") from None
+    except (KeyError, AttributeError):
+        what = getattr(t, "dtype", type(t).__name__)
+        raise BlurB200Error(_lib.EINVAL, f"element type {what} is not one of uint8 / uint16 / int32 / float32") from None
+
+
+def _elem_bytes(t) -> int:
+    """Bytes per element of a torch tensor (element_size()) or of anything with an itemsize (numpy, cupy)."""
+    if hasattr(t, "element_size"):
+        return int(t.element_size())
+    if hasattr(t, "itemsize"):
+        return int(t.itemsize)
+    raise BlurB200Error(_lib.EINVAL, f"cannot tell the element size of a {type(t).__name__}")
 
 
 def deinterleave_BGR(d_interleaved, d_planes, total: int, stream: int | None = None) -> None:
     """deinterleave_BGR<T,U>, Utils.hpp:159-184: d_planes[c][x] = (U)(d_interleaved[3x+c] + round), round = 0.5f only
     for floating -> integral.  T, U from the tensors' dtypes (uint8 / uint16 / int32 / float32); the blur's own
-    instantiation is <uint8_t,float>.  d_planes: CUDA tensor [3, total]."""
+    instantiation is <uint8_t,float>.  d_planes: CUDA tensor [3, total], or a list / tuple of three plane tensors."""
     check(lib.blur_b200_deinterleave_typed(_ptr(d_interleaved), _ptr(d_planes[0]), _ptr(d_planes[1]), _ptr(d_planes[2]), total,
                                            _type_code(d_interleaved), _type_code(d_planes),
                                            _stream() if stream is None else stream))
@@ -365,7 +378,7 @@ def interleave_BGR(d_planes, d_interleaved, total: int, stream: int | None = Non
 def flip_block(d_in, d_out, w: int, h: int, stream: int | None = None, channels: int = 1) -> None:
     """flip_block<T,C>(in, out, w, h): in is h x w pixels of C elements, out is w x h (Source.cpp:540,562 call
     it as <float,1>)."""
-    check(lib.blur_b200_flip_block_pixels(_ptr(d_in), _ptr(d_out), w, h, channels * d_in.element_size(),
+    check(lib.blur_b200_flip_block_pixels(_ptr(d_in), _ptr(d_out), w, h, channels * _elem_bytes(d_in),
                                           _stream() if stream is None else stream))
 
 

@@ -310,3 +310,20 @@ def test_sweep_plot_tool(tmp_path):
     assert len(paths) >= 4
     text = out.read_text()
     assert "B200 pffft_ device-resident" in text and "B200 pocketfft_1D host call" in text
+
+
+def test_api_type_helpers_accept_plane_lists_and_numpy():
+    """deinterleave_BGR / interleave_BGR take a [3, total] tensor or a list / tuple of three planes; flip_block takes
+    anything with element_size() or itemsize; everything else is a BlurB200Error, never an AttributeError."""
+    import torch
+    from blur_algorithms_b200 import api
+    planes = [torch.zeros(4, dtype=torch.float32) for _ in range(3)]
+    assert api._type_code(planes) == 3 and api._type_code(tuple(planes)) == 3
+    assert api._type_code(torch.zeros((3, 4), dtype=torch.uint8)) == 0
+    assert api._type_code(np.zeros(3, np.int32)) == 2
+    assert api._elem_bytes(np.zeros(3, np.float32)) == 4 and api._elem_bytes(torch.zeros(3, dtype=torch.uint16)) == 2
+    for bad in ([object()], torch.zeros(3, dtype=torch.float64), 7):
+        with pytest.raises(api.BlurB200Error):
+            api._type_code(bad)
+    with pytest.raises(api.BlurB200Error):
+        api._elem_bytes(object())
