@@ -118,7 +118,7 @@ class ClockSampler:
 
 # ------------------------------------------------------------------------------------------ CPU reference
 
-def cpu_reference_run(wl: dict, steps: int, warmup: int):
+def cpu_reference_run(wl: dict, steps: int, warmup: int, nyquist: str = "exact"):
     """Times the reference's own pipeline on the host cores: oracle/_ref (Source.cpp + Utils.hpp compiled
     unmodified) when it was built, else the C restatement.  FULL-SIZE steps of the workload (box: a bounded
     number of the batch's images); the OpenMP thread count is set here to every host core (torchrun exports
@@ -133,15 +133,18 @@ def cpu_reference_run(wl: dict, steps: int, warmup: int):
     impl.set_num_threads(cores)
     threads = impl.num_threads()
     assert threads == cores or cores == 1, (threads, cores)
-    engine = "FFT engine = this repo's scalar C mixed-radix FFT (oracle/cpu_fft.c) standing in for the absent SIMD pffft"
+    engine = "FFT engine = this repo's scalar C mixed-radix FFT (oracle/cpu_fft.c) standing in for the absent pffft / pocketfft"
     if wl["kind"] == "gauss":
         img = rng.integers(0, 256, (rows, cols, 3), dtype=np.uint8)
+        # the same function as the GPU arm: exact multiply = pocketfft_1D (Test flag 5, Source.cpp:580-581),
+        # pffft's Nyquist quirk = pffft_ (Test flag 3, :589-590)
+        flag, fname, mode = (5, "pocketfft_1D", 0) if nyquist == "exact" else (3, "pffft_", 1)
         if use_ref:
-            fn = lambda: impl.test(img, 3, wl["sigma"])                 # noqa: E731  Test(flag=3) -> pffft_
-            what = "Source.cpp Test(flag=3) -> pffft_() compiled unmodified (OpenMP) against API shims; " + engine
+            fn = lambda: impl.test(img, flag, wl["sigma"])              # noqa: E731
+            what = f"Source.cpp Test(flag={flag}) -> {fname}() compiled unmodified (OpenMP) against API shims; " + engine
         else:
-            fn = lambda: impl.gauss_blur_1d(img, wl["sigma"], 1)        # noqa: E731
-            what = "C restatement of pffft_() (oracle/blur_oracle.c, OpenMP); " + engine
+            fn = lambda: impl.gauss_blur_1d(img, wl["sigma"], mode)     # noqa: E731
+            what = f"C restatement of {fname}() (oracle/blur_oracle.c, OpenMP); " + engine
         mpx = rows * cols / 1e6
         sample = f"{rows}x{cols} RGB, sigma={wl['sigma']:g}: the whole workload image per step"
     else:
@@ -213,6 +216,10 @@ def main() -> None:
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-verify", action="store_true")
+    ap.add_argument("--no-halo", action="store_true", help="N > 1 gauss: skip the row-stripe (halo) sharding line printed beside the contract one")
+    ap.add_argument("--sharding", default="contract", choices=["contract", "halo"],
+                    help="N > 1 gauss: which sharding `value` reports; contract = row stripes -> all-to-all -> column stripes "
+                         "(BASELINE.json), halo = row stripes in, row stripes out, 2*halo rows exchanged (the other one is printed beside it)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -224,12 +231,24 @@ def main() -> None:
     if wl["kind"] == "gauss":
         config = {"workload": f"gauss_blur_{rows}x{cols}_rgb_u8_sigma{wl['sigma']:g}", "rows": rows, "cols": cols,
                   "sigma": wl["sigma"], "nyquist_mode": args.nyquist,
-                  "sharding": "single GPU" if args.gpus == 1 else f"one image: row stripes x{args.gpus} -> exchange -> column stripes"}
+                  "sharding": "single GPU" if args.gpus == 1 else
+                              (f"one image: row stripes x{args.gpus} in and out, halo rows exchanged" if args.sharding == "halo" else
+                               f"one image: row stripes x{args.gpus} -> exchange -> column stripes")}
     else:
         config = {"workload": f"fastboxblur_{wl['batch']}x{rows}x{cols}_rgb_u8_ksize{wl['ksize']}_passes{wl['passes']}",
                   "rows": rows, "cols": cols, "ksize": wl["ksize"], "passes": wl["passes"], "batch": wl["batch"],
                   "sharding": "single GPU" if args.gpus == 1 else f"image i -> rank i mod {args.gpus}, no collective",
                   "parity": "bit-exact against the declared spec (SURVEY A.7); upstream FastBoxBlur absent: parity unpinned"}
+    # `config` names the workload and is the same dict in both arms (the driver compares them); what only one arm
+    # can say (exchange variant, CPU engine, threads) goes into the line's "run" object
+    if wl["kind"] == "gauss":
+        small = rows * cols * 15 < 200e6                 # working set near the 126 MB L2: flush between steps
+        config["l2_policy"] = ("L2 flushed (256 MB write) before every timed step" if small else
+                               "inputs larger than L2 (%d MB image, %.1f GB float32 intermediate)" % (rows * cols * 3 // 1000000, rows * cols * 12 / 1e9))
+    else:
+        per_rank = -(-wl["batch"] // max(args.gpus, 1)) * rows * cols * 3
+        config["l2_policy"] = "per-rank batch (%d MB) larger than L2" % (per_rank >> 20)
+    run_info = {}
     metric = METRICS[wl["kind"]] if wl["kind"] == "box" or wl.get("sigma") == 50.0 else f"megapixels/sec RGB Gaussian blur (sigma={wl['sigma']:g})"
     scaling = "strong"          # gauss: one image cut over the ranks; box: one fixed batch dealt over the ranks
 
@@ -237,14 +256,14 @@ def main() -> None:
         if rank != 0:
             return
         K, W = max(1, args.steps), max(0, args.warmup)
-        base, dt, mpx = cpu_reference_run(wl, K, W)
-        config["engine"] = "scalar C stand-in for pffft / FastBoxBlur (submodules absent)"
-        config["sample"] = base["sample"].split(";")[0]
-        config["threads"] = base["cores"]
+        base, dt, mpx = cpu_reference_run(wl, K, W, args.nyquist)
+        run_info["engine"] = "scalar C stand-in for pffft / pocketfft / FastBoxBlur (submodules absent)"
+        run_info["sample"] = base["sample"].split(";")[0]
+        run_info["threads"] = base["cores"]
         line = {"metric": metric, "value": base["value"], "unit": "megapixels/sec", "n_gpus": args.gpus, "steps": K,
                 "warmup": W, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": scaling,
                 "vs_baseline": None, "dtype": "f32" if wl["kind"] == "gauss" else "u8", "data": "synthetic", "config": config,
-                "impl": "reference", "cpu_baseline": base,
+                "impl": "reference", "run": run_info, "cpu_baseline": base,
                 "e2e": {"value": base["value"], "unit": "megapixels/sec", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
         print(json.dumps(line))
@@ -296,9 +315,7 @@ def main() -> None:
         nyq = bb.NYQUIST_PFFFT if args.nyquist == "pffft" else bb.NYQUIST_EXACT
         lsb_tol = 1 if args.nyquist == "exact" else 16    # pffft_'s Nyquist term moves uniform noise by several LSB off the exact convolution
         npx = rows * cols
-        small = rows * cols * 15 < 200e6                 # working set near the 126 MB L2: flush between steps
-        config["l2_policy"] = ("L2 flushed (256 MB write) before every timed step" if small else
-                               "inputs larger than L2 (805 MB image, 3.2 GB float32 intermediate)")
+        small = config["l2_policy"].startswith("L2 flushed")
         if small:
             flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
         full_img = None
@@ -318,8 +335,19 @@ def main() -> None:
             h_img = torch.from_numpy(np.ascontiguousarray(full_img[g.row0:g.row0 + g.valid_rows])).pin_memory()
             d_in = h_img.to(dev)
             plan = sb.plan
-            config["exchange"] = sb.describe_exchange()
             step = lambda: sb.run(d_in)                      # noqa: E731
+            # row-stripe (halo) sharding beside it: input and output row-sharded, only 2*halo rows of the float32
+            # intermediate cross NVLink (dist.HaloShardedGaussBlur); exact mode, two-factor kernels
+            hb = d_in_h = None
+            if args.nyquist == "exact" and not args.no_halo:
+                from blur_algorithms_b200.dist import HaloShardedGaussBlur
+                try:
+                    hb = HaloShardedGaussBlur(rows, cols, sigma, device=dev)
+                    d_in_h = torch.from_numpy(np.ascontiguousarray(full_img[hb.row0:hb.row0 + hb.valid_rows])).to(dev)
+                except ValueError as ex:
+                    hb = None
+                    line_extra["halo"] = {"unavailable": str(ex)}
+            halo_ok = None
 
         # ---- verification, outside every timed region
         verified = None
@@ -338,7 +366,7 @@ def main() -> None:
                 del out
             else:
                 # this rank's column stripe of the sharded result == the single-GPU plan's, bit for bit
-                p1 = bb.GaussPlan(rows, cols, sigma, nyq, device=local)
+                p1 = bb.GaussPlan(rows, cols, sigma, nyq, device=local, direct=False)   # FFT kernels like the sharded plans
                 d_full = torch.from_numpy(full_img).to(dev)
                 p1.run(d_full)
                 mine = sb.run(d_in)
@@ -354,6 +382,10 @@ def main() -> None:
                 ok = allmin_int(int(same and dmax <= lsb_tol))
                 verified = {"ok": bool(ok), "check": "every rank: its column stripe bit-identical to the single-GPU plan's output, "
                             "plus 8 pixels per rank against a float64 direct convolution (+-1 LSB)", "max_abs_diff_lsb": allmax(dmax)}
+                if hb is not None:
+                    got = hb.run(d_in_h)
+                    torch.cuda.synchronize()
+                    halo_ok = bool(allmin_int(int(torch.equal(got, d_full[hb.row0:hb.row0 + hb.valid_rows]))))
                 p1.close()
                 del d_full
         del full_img
@@ -361,6 +393,11 @@ def main() -> None:
         # ---- device-resident timing
         for _ in range(W):
             step()
+        if multi:
+            # the exchange variant is chosen by a timed trial on the first blur (dist.ShardedGaussBlur.tune_exchange)
+            run_info["exchange"] = sb.describe_exchange()
+            run_info["exchange_mode"] = sb.exchange_mode if sb.fused else "nccl"
+            run_info["exchange_trial_ms"] = sb.exchange_trial
         barrier()
         sampler = ClockSampler(local)
         sampler.start()
@@ -389,6 +426,27 @@ def main() -> None:
         clocks = sampler.stop()
         ms_per_step = allmax(ms) / K
         value = npx / 1e6 / (ms_per_step * 1e-3)
+        if multi and hb is not None:
+            for _ in range(W):
+                hb.run(d_in_h)
+            barrier()
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            ev0.record(stream)
+            for _ in range(K):
+                hb.run(d_in_h)
+            ev1.record(stream)
+            barrier()
+            hms = allmax(ev0.elapsed_time(ev1)) / K
+            line_extra["halo"] = {
+                "ms_per_step": hms, "value": npx / 1e6 / (hms * 1e-3), "unit": "megapixels/sec",
+                "sharding": "row stripes of whole column-pass blocks in AND out; every rank pushes 2*halo rows of the float32 "
+                            "intermediate to its two neighbours (copy engines over NVLink), no all-to-all",
+                "halo_rows": hb.info["halo"], "exchanged_bytes_per_gpu": 2 * hb.info["halo"] * cols * 12,
+                "verified": None if halo_ok is None else {"ok": halo_ok, "check": "every rank: its row stripe bit-identical to the single-GPU plan's output"}}
+            line_extra["contract"] = {"ms_per_step": ms_per_step, "value": value, "unit": "megapixels/sec"}
+            if args.sharding == "halo":
+                ms_per_step, value = hms, line_extra["halo"]["value"]
 
         # ---- per-pass timing for the roofline (same stream, CUDA events)
         e = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
@@ -528,7 +586,6 @@ def main() -> None:
         d_img = torch.empty_like(d_src)
         d_scr = torch.empty_like(d_src)
         npx = batch * rows * cols
-        config["l2_policy"] = "per-rank batch (%d MB) larger than L2" % (d_src.numel() >> 20)
 
         def step():
             d_img.copy_(d_src)                             # the blur is in place: restore the input (device copy, inside the step)
@@ -590,13 +647,13 @@ def main() -> None:
 
     cpu = None
     if rank == 0 and not multi and not args.no_cpu_baseline:
-        cpu, _, _ = cpu_reference_run(wl, 2, 1)
+        cpu, _, _ = cpu_reference_run(wl, 2, 1, args.nyquist)
 
     if rank == 0:
         line = {"metric": metric, "value": value, "unit": "megapixels/sec", "n_gpus": args.gpus, "steps": K, "warmup": W,
                 "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": scaling, "vs_baseline": None,
                 "dtype": dtype, "data": "synthetic", "config": config, "roofline": roofline, "clocks": clocks,
-                "e2e": e2e, "gpu_launches": int(launches), "impl": "b200", "verified": verified}
+                "e2e": e2e, "gpu_launches": int(launches), "impl": "b200", "run": run_info, "verified": verified}
         line.update(line_extra)
         if cpu is not None:
             line["cpu_baseline"] = cpu

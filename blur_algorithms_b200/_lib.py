@@ -45,6 +45,7 @@ def _load() -> C.CDLL:
         "blur_b200_gauss_plan_destroy": (None, [vp]),
         "blur_b200_gauss_plan_info": (i32, [vp, C.POINTER(C.c_int64)]),
         "blur_b200_gauss_plan_uses_direct": (i32, [vp]),
+        "blur_b200_gauss_plan_set_direct": (i32, [vp, i32]),
         "blur_b200_gauss_run_device": (i32, [vp, vp, vp, vp]),
         "blur_b200_gauss_run_host": (i32, [vp, vp, vp]),
         "blur_b200_gauss_run_host_batch": (i32, [vp, C.POINTER(vp), C.POINTER(vp), i32]),
@@ -104,7 +105,7 @@ EXPORTED = [
     "blur_b200_strerror", "blur_b200_last_cuda_error", "blur_b200_is_valid_size",
     "blur_b200_nearest_transform_size", "blur_b200_gaussian_window", "blur_b200_get_gaussian",
     "blur_b200_gauss_geometry", "blur_b200_gauss_shard_geometry", "blur_b200_gauss_plan_create", "blur_b200_gauss_plan_create_sharded",
-    "blur_b200_gauss_plan_destroy", "blur_b200_gauss_plan_info", "blur_b200_gauss_plan_uses_direct", "blur_b200_gauss_run_device",
+    "blur_b200_gauss_plan_destroy", "blur_b200_gauss_plan_info", "blur_b200_gauss_plan_uses_direct", "blur_b200_gauss_plan_set_direct", "blur_b200_gauss_run_device",
     "blur_b200_gauss_run_host", "blur_b200_gauss_run_host_batch", "blur_b200_gauss_u8c3", "blur_b200_release_cached", "blur_b200_gauss_row_pass",
     "blur_b200_gauss_col_pass", "blur_b200_gauss_row_pass_peer", "blur_b200_gauss_row_pass_push", "blur_b200_boxfft_klen", "blur_b200_boxfft_plan_create", "blur_b200_boxfft_u8c3",
     "blur_b200_gauss_halo_info", "blur_b200_gauss_halo_row_pass", "blur_b200_gauss_halo_push", "blur_b200_gauss_halo_col_pass",

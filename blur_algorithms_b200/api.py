@@ -124,9 +124,12 @@ class GaussPlan:
     one (rows, cols, sigma) problem.  Replaces the per-call setup of Source.cpp:465-503."""
 
     def __init__(self, rows: int, cols: int, sigma: float, nyquist_mode: int = NYQUIST_EXACT,
-                 device: int = 0, rank: int = 0, nranks: int = 1, boxblur: bool = False):
+                 device: int = 0, rank: int = 0, nranks: int = 1, boxblur: bool = False, direct: bool | None = None):
         """boxblur=True: the reference's `#define boxblur` build — `sigma` is then its nsmooth and the kernel a box
-        of width kLen = boxfft_klen(rows, cols, nsmooth) convolved with itself (Source.cpp:128-140, 287-291)."""
+        of width kLen = boxfft_klen(rows, cols, nsmooth) convolved with itself (Source.cpp:128-140, 287-291).
+        direct=False: a single-GPU plan of a narrow kernel (half width <= 20) keeps the FFT kernels for run() /
+        run_host*() instead of the fused direct kernel, so that its output equals the sharded, halo and pass-wise
+        results bit for bit (the two kernel families agree within 1 LSB only)."""
         self._h = C.c_void_p()
         self.rows, self.cols, self.sigma = rows, cols, float(sigma)
         self.rank, self.nranks = rank, nranks
@@ -146,6 +149,10 @@ class GaussPlan:
                 "algo", "ols_L_row", "ols_L_col", "ols_V_row", "ols_V_col", "ols_nblocks_row", "ols_nblocks_col", "rqs"]
         self.info = {k: int(v) for k, v in zip(keys, info)}
         # whole-image entries on the fused direct-convolution kernel (narrow kernels, single GPU)
+        if direct is not None and (not direct or lib.blur_b200_gauss_plan_uses_direct(self._h) == 0):
+            if direct and nranks != 1:
+                raise BlurB200Error(_lib.EINVAL, "the direct kernel is a single-GPU path")
+            check(lib.blur_b200_gauss_plan_set_direct(self._h, int(bool(direct))))
         self.info["direct"] = int(lib.blur_b200_gauss_plan_uses_direct(self._h))
 
     def close(self) -> None:

@@ -995,12 +995,14 @@ int blur_b200_gauss_shard_geometry(int rows, int cols, double sigma, int nyquist
 
 int blur_b200_gauss_plan_create(blur_b200_plan** plan, int rows, int cols, double sigma, int nyquist_mode, int device)
 {
+    if (!(sigma > 0)) return BLUR_B200_EINVAL;      // the negative encoding of the FFT box blur is internal (blur_b200_boxfft_*)
     return plan_create(plan, rows, cols, sigma, nyquist_mode, device, 0, 1);
 }
 
 int blur_b200_gauss_plan_create_sharded(blur_b200_plan** plan, int rows, int cols, double sigma, int nyquist_mode,
                                         int device, int rank, int nranks)
 {
+    if (!(sigma > 0)) return BLUR_B200_EINVAL;
     return plan_create(plan, rows, cols, sigma, nyquist_mode, device, rank, nranks);
 }
 
@@ -1080,6 +1082,14 @@ static int run_direct(blur_b200_plan* p, const uint8_t* d_in, uint8_t* d_out, cu
 }
 
 int blur_b200_gauss_plan_uses_direct(const blur_b200_plan* p) { return p && p->direct ? 1 : 0; }
+
+int blur_b200_gauss_plan_set_direct(blur_b200_plan* p, int enable)
+{
+    if (!p) return BLUR_B200_EINVAL;
+    if (enable && !p->d_dtaps) return BLUR_B200_ESIZE;     // this plan was built without the direct kernel's taps
+    p->direct = enable != 0;
+    return BLUR_B200_OK;
+}
 
 int blur_b200_gauss_run_device(blur_b200_plan* p, const uint8_t* d_in, uint8_t* d_out, void* stream)
 {

@@ -160,7 +160,8 @@ class ShardedBatch:
 
 
 class ShardedGaussBlur:
-    """One rank's half of the sharded blur.  `row_pass(in_stripe, q_send)` and
+    """One rank's half of the sharded blur.  Every rank's column stripe equals the single-GPU plan's output bit for
+    bit when that plan runs the FFT kernels (always for half widths > 20; GaussPlan(..., direct=False) below that).  `row_pass(in_stripe, q_send)` and
     `col_pass(q_recv, out_cols)` default to the CUDA plan; tests may inject CPU stand-ins."""
 
     def __init__(self, rows: int, cols: int, sigma: float, nyquist_mode: int = 0, group=None,
@@ -175,11 +176,13 @@ class ShardedGaussBlur:
         nfl = self.nranks * g.block_floats
         self.plan = None
         self.symm = None
-        # "push": row pass in chunks + copy kernel over peer mappings (default); "store": the row
-        # kernel's epilogue stores remotely itself.  BLUR_B200_EXCHANGE overrides.
-        # measured defaults (profiles/r02_exchange_modes.txt): up to 4 GPUs the copy-engine sub-range pipeline hides the
-        # exchange behind the FFTs; beyond that the SM-issued bulk stores carry more all-to-all bandwidth
-        self.exchange_mode = exchange_mode or os.environ.get("BLUR_B200_EXCHANGE") or ("staged" if self.nranks <= 4 else "store")
+        # "push": row pass in chunks + copy engines over peer mappings; "store": the row kernel's epilogue stores
+        # remotely itself; "staged": column sub-ranges pushed by the copy engines under the next sub-range's FFTs.
+        # Which one wins depends on the box, not only on N (staged at N=4: 1.44 ms on an 8-GPU box, 2.4 ms on two
+        # 4-GPU boxes; store 1.62, push 1.70), so the default "auto" times them on the first blur (tune_exchange)
+        # and keeps the fastest.  An explicit exchange_mode / BLUR_B200_EXCHANGE skips the trial.
+        self.exchange_mode = exchange_mode or os.environ.get("BLUR_B200_EXCHANGE") or "auto"
+        self.exchange_trial = None                       # {mode: ms per blur, max over ranks} once tune_exchange has run
         self.nchunks = nchunks or int(os.environ.get("BLUR_B200_CHUNKS", "0")) or {2: 12}.get(self.nranks, 2)
         self.nstages = int(os.environ.get("BLUR_B200_STAGES", "0")) or 4
         # sstore: CTAs per SM of the row launches / of the column launches that run beside them
@@ -214,16 +217,44 @@ class ShardedGaussBlur:
             row_pass = self.plan.row_pass
             col_pass = self.plan.col_pass
         self._row_pass, self._col_pass = row_pass, col_pass
+        self._check_geometry()
         # pffft mode on the overlap-save path: two small correction buffers are summed over the ranks per blur
         self._quirk = self.plan.quirk_buffers() if (self.plan is not None and nyquist_mode != 0 and g.algo == 1 and self.nranks > 1) else None
         if self._quirk is not None and self.exchange_mode == "sstore":
             self.exchange_mode = "staged"                # the second stream would not see quirk_finish
-        if self.exchange_mode in ("staged", "sstore"):
-            # fewer stages if the part does not divide, plain push if the plan cannot run staged at all
-            while self.nstages > 1 and not (self.plan is not None and self.symm is not None and self.plan.staged_supported(self.nstages)):
-                self.nstages //= 2
-            if self.plan is None or self.symm is None or not self.plan.staged_supported(self.nstages):
-                self.exchange_mode = "push"
+        # fewer stages if the part does not divide; the plan may not be able to run staged at all
+        can_stage = self.plan is not None and self.symm is not None
+        while can_stage and self.nstages > 1 and not self.plan.staged_supported(self.nstages):
+            self.nstages //= 2
+        self._can_stage = bool(can_stage and self.plan.staged_supported(self.nstages))
+        if self.exchange_mode in ("staged", "sstore") and not self._can_stage:
+            self.exchange_mode = "push"
+        self._auto = self.exchange_mode == "auto"
+        if self._auto:
+            # until the trial has run (or where there is nothing to choose: no peer memory) the pair-major store
+            self.exchange_mode = "store"
+            self._auto = self.symm is not None and self.plan is not None
+
+    def _check_geometry(self) -> None:
+        """The layout of the exchanged intermediate is decided on the C side (shard_geometry), partly from
+        BLUR_B200_* experiment knobs in the environment.  A rank whose environment differs, or a knob that changed
+        between the geometry query and the plan's creation, would address the exchange buffers differently and
+        corrupt them silently: compare the plan with the geometry, and the ranks with each other, once."""
+        g = self.geom
+        sig = (g.algo, g.stripe_rows, g.cpp, g.block_floats, g.qpitch)
+        if self.plan is not None:
+            i = self.plan.info
+            mine = (i["algo"], i["stripe_rows"], i["cpp"], i["block_floats"])
+            if mine != sig[:4]:
+                raise RuntimeError(f"rank {self.rank}: plan layout {mine} differs from blur_b200_gauss_shard_geometry {sig[:4]} "
+                                   "(BLUR_B200_* environment changed between the two calls?)")
+            sig += (i["ols_L_row"], i["ols_V_row"], i["ols_L_col"], i["ols_V_col"], i["ols_nblocks_row"], i["ols_nblocks_col"])
+        if self.nranks > 1 and dist.is_initialized():
+            sigs = [None] * self.nranks
+            dist.all_gather_object(sigs, sig, group=self.group)
+            if any(tuple(x) != tuple(sigs[0]) for x in sigs):
+                raise RuntimeError(f"sharded blur: the ranks disagree on the layout of the intermediate: {sigs} "
+                                   "(the BLUR_B200_* environment must be the same on every rank)")
 
     @property
     def fused(self) -> bool:
@@ -248,6 +279,34 @@ class ShardedGaussBlur:
         return (f"row pass in {self.nchunks} wave-aligned chunks; copy engines (cudaMemcpy2DAsync peer copies, one per "
                 "destination and chunk) move each finished chunk from a local send buffer into the owners' "
                 "symmetric-memory buffers under the next chunk's FFTs")
+
+    def tune_exchange(self, in_stripe: torch.Tensor, candidates=("store", "staged", "push"), steps: int = 3) -> dict:
+        """Collective: every rank times `steps` whole blurs of `in_stripe` per exchange variant (after one untimed
+        blur each; CUDA events, MAX over ranks so that all ranks see the same numbers), keeps the fastest and
+        returns {mode: ms per blur}.  Called by the first run() when the mode was left to "auto"; callers that
+        build many plans of one geometry can pass the winner as exchange_mode to the next ones."""
+        self._auto = False
+        if self.symm is None or self.plan is None:
+            return {}
+        stream = torch.cuda.current_stream(self.device)
+        trial = {}
+        for mode in candidates:
+            if mode in ("staged", "sstore") and (not self._can_stage or (mode == "sstore" and self._quirk is not None)):
+                continue
+            self.exchange_mode = mode
+            self._rows(in_stripe); self._cols()
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ev0.record(stream)
+            for _ in range(steps):
+                self._rows(in_stripe); self._cols()
+            ev1.record(stream)
+            ev1.synchronize()
+            t = torch.tensor([ev0.elapsed_time(ev1) / steps], dtype=torch.float32, device=self.device)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX, group=self.group)
+            trial[mode] = round(float(t.item()), 4)
+        self.exchange_mode = min(trial, key=trial.get)      # same dict on every rank: same choice
+        self.exchange_trial = trial
+        return trial
 
     def row_pass_only(self) -> None:
         """The row phase as run() issues it, without the two barriers (per-pass timing in bench.py)."""
@@ -277,6 +336,8 @@ class ShardedGaussBlur:
         """in_stripe: uint8 [valid_rows, cols, 3] (this rank's rows).  Returns this rank's column
         stripe of the result, uint8 [rows, valid_cols, 3] (a view into an internal buffer) — or, with
         row_sharded=True, this rank's ROW stripe [valid_rows, cols, 3] after the return exchange."""
+        if self._auto:
+            self.tune_exchange(in_stripe)
         self._rows(in_stripe)
         out = self._cols()
         return self.to_row_stripe() if row_sharded else out
@@ -378,6 +439,8 @@ class ShardedGaussBlur:
         if len(h_ins) != len(h_outs):
             raise ValueError("h_ins and h_outs must have the same length")
         cur = torch.cuda.current_stream(self.device)
+        if self._auto and len(h_ins):
+            self.tune_exchange(h_ins[0].to(self.device))
         if not hasattr(self, "_s_up"):
             self._s_up = torch.cuda.Stream(self.device)
             self._s_dn = torch.cuda.Stream(self.device)
@@ -414,7 +477,8 @@ class HaloShardedGaussBlur:
     blocks, runs the row pass on it, pushes its first / last `halo` rows of the float32 intermediate into the two
     neighbours' buffers (symmetric memory over NVLink, two copy-engine copies) and runs the column pass on its own
     blocks: 2 * halo * cols * 12 bytes per GPU on the wire instead of rows * cols * 12 * (P - 1) / P^2, no all-to-all,
-    result bit-identical to the single-GPU plan.  Exact mode, kernels narrow enough for the two-factor blocks."""
+    result bit-identical to the single-GPU plan's FFT kernels (GaussPlan(..., direct=False) for kernels of half width
+    <= 20, whose whole-image entries otherwise take the direct kernel: +-1 LSB).  Exact mode, kernels narrow enough for the two-factor blocks."""
 
     def __init__(self, rows: int, cols: int, sigma: float, group=None, device: torch.device | None = None):
         from .api import GaussPlan
@@ -422,7 +486,8 @@ class HaloShardedGaussBlur:
         self.rank = dist.get_rank(group) if dist.is_initialized() else 0
         self.nranks = dist.get_world_size(group) if dist.is_initialized() else 1
         self.device = device if device is not None else torch.device("cuda", torch.cuda.current_device())
-        self.plan = GaussPlan(rows, cols, sigma, 0, device=self.device.index or 0)
+        # direct=False: plan.run() of the whole image then uses the same FFT kernels as the halo entries (bit-identical)
+        self.plan = GaussPlan(rows, cols, sigma, 0, device=self.device.index or 0, direct=False)
         info = self.plan.halo_info(self.rank, self.nranks)
         if info is None:
             raise ValueError("this geometry cannot run row-stripe sharded (needs the two-factor kernels on both axes)")

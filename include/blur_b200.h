@@ -103,6 +103,12 @@ int blur_b200_gauss_run_device(blur_b200_plan *plan, const uint8_t *d_in, uint8_
  * (sigma <= ~6.3; BASELINE config 1).  Same convolution (reflect-101, the float taps of getGaussian,
  * Source.cpp:75-102), evaluated tap by tap in fp32; the pass-wise entries below always use the FFT kernels. */
 int blur_b200_gauss_plan_uses_direct(const blur_b200_plan *plan);
+/* enable = 0: the whole-image entries of this plan use the two FFT passes from now on, like the pass-wise, sharded and
+ * halo entries always do.  The direct kernel and the FFT kernels agree within 1 LSB, not bit for bit: turn the direct
+ * kernel off on the single-GPU plan whenever its output is compared byte for byte with a sharded or pass-wise result of
+ * a narrow kernel (half width <= 20).  enable = 1 switches it back on (BLUR_B200_ESIZE if the plan never had it).
+ * No counterpart in the reference. */
+int blur_b200_gauss_plan_set_direct(blur_b200_plan *plan, int enable);
 
 /* Whole blur on host buffers (pinned or pageable); H2D + kernels + D2H.  In place allowed. */
 int blur_b200_gauss_run_host(blur_b200_plan *plan, const uint8_t *h_in, uint8_t *h_out);

@@ -155,6 +155,7 @@ def test_gauss_float32_intermediate_c2_c3(bb, oracle, torch, rows, cols, sigma, 
               f"max err / max(|ref|, 1) {rel:.3e}; block length L = {plan.info['ols_L_row']}")
     plan.close()
     assert err <= F32_TOL
+    assert rel <= 1e-5          # and in the relative reading: |got - ref| <= 1e-5 * max(|ref|, 1) everywhere
 
 
 def test_gauss_sharded_multi_gpu_bit_identity():
@@ -190,7 +191,10 @@ def test_gauss_float32_intermediate(bb, oracle, torch):
         d_pl = torch.empty((3, rows, cols), dtype=torch.float32, device="cuda")
         plan.rowpass_f32(d_in, d_pl)
         torch.cuda.synchronize()
-        assert np.abs(d_pl.cpu().numpy() - rp).max() <= F32_TOL
+        got = d_pl.cpu().numpy()
+        assert np.abs(got - rp).max() <= F32_TOL
+        # the relative reading of "within 1e-5": relative to max(|ref|, 1) for every element
+        assert (np.abs(got - rp) / np.maximum(np.abs(rp), 1.0)).max() <= 1e-5
         plan.close()
 
 
@@ -240,14 +244,19 @@ def test_gauss_errors(bb):
     with pytest.raises(bb.BlurB200Error) as e:
         bb.pffft_(synth("noise", 16, 400), 50.0)      # pad 165 > rows-1: reference would read OOB
     assert e.value.code == 2
-    with pytest.raises(bb.BlurB200Error):
-        bb.GaussPlan(64, 64, -1.0)
+    for bad in (-1.0, -5.0, -4.6, 0.0):      # -5 / -4.6 are the internal encoding of an FFT box blur: not reachable from gauss_*
+        with pytest.raises(bb.BlurB200Error) as e:
+            bb.GaussPlan(64, 64, bad)
+        assert e.value.code == 1
+        with pytest.raises(bb.BlurB200Error):
+            bb.GaussPlan(64, 64, bad, rank=0, nranks=2)
+        with pytest.raises(bb.BlurB200Error):
+            bb.pocketfft_1D(synth("noise", 64, 64), bad)
 
 
 def test_gauss_sharded_emulated_on_one_gpu(bb, torch, monkeypatch):
     """P ranks' plans executed one after another on one GPU with the all-to-all done by copies:
     bit-identical to the single-plan result (SURVEY.md §4 multi-GPU test plan)."""
-    monkeypatch.setenv("BLUR_B200_DIRECT", "0")       # narrow kernels: the single-GPU plan would take the direct kernel, the sharded ones cannot
     for rows, cols, sigma, mode, P in [(135, 241, 6.0, 1, 3), (240, 320, 5.0, 0, 2), (256, 256, 3.0, 0, 8)]:
         if mode == 1:
             monkeypatch.setenv("BLUR_B200_QUIRK_SHARDED", "full")      # round 1's sharded pffft path: the full-length kernel
@@ -255,7 +264,8 @@ def test_gauss_sharded_emulated_on_one_gpu(bb, torch, monkeypatch):
             monkeypatch.delenv("BLUR_B200_QUIRK_SHARDED", raising=False)
         img = synth("noise", rows, cols, 6)
         single = torch.from_numpy(img).cuda()
-        p1 = bb.GaussPlan(rows, cols, sigma, mode)
+        p1 = bb.GaussPlan(rows, cols, sigma, mode, direct=False)   # narrow kernels: FFT kernels, like the sharded plans
+        assert p1.info["direct"] == 0
         p1.run(single)
         plans = [bb.GaussPlan(rows, cols, sigma, mode, rank=r, nranks=P) for r in range(P)]
         bf = plans[0].info["block_floats"]
@@ -655,11 +665,10 @@ def test_gauss_halo_sharding_emulated_on_one_gpu(bb, torch, monkeypatch):
     """Row-stripe (halo) sharding, all ranks emulated on one GPU with the halo pushes as same-device copies: stripes of
     whole column blocks, 2 * halo rows exchanged, output row-sharded and bit-identical to the single-GPU plan —
     including a short last stripe, empty trailing ranks and image-edge blocks."""
-    monkeypatch.setenv("BLUR_B200_DIRECT", "0")
     for rows, cols, sigma, P in [(4096, 1024, 50.0, 4), (3000, 777, 25.0, 2), (2200, 640, 30.0, 8), (1500, 1000, 9.0, 3), (5300, 512, 50.0, 8)]:
         img = synth("noise", rows, cols, 13)
         d_img = torch.from_numpy(img).cuda()
-        plan = bb.GaussPlan(rows, cols, sigma, 0)
+        plan = bb.GaussPlan(rows, cols, sigma, 0, direct=False)
         want = plan.run(d_img, torch.empty_like(d_img))
         infos = [plan.halo_info(r, P) for r in range(P)]
         assert all(i is not None for i in infos), (rows, cols, sigma)
@@ -731,6 +740,12 @@ def test_gauss_direct_kernel_narrow_kernels(bb, oracle, torch, monkeypatch):
             dd = np.abs(fft.astype(int) - out.astype(int))
             assert dd.max() <= 1 and (dd > 0).mean() < 1e-3, (rows, cols, sigma, mode, float((dd > 0).mean()))
             pf.close()
+            # the plan-level switch (blur_b200_gauss_plan_set_direct) gives the same two results without the environment
+            monkeypatch.delenv("BLUR_B200_DIRECT", raising=False)
+            ps = bb.GaussPlan(rows, cols, sigma, mode, direct=False)
+            assert ps.info["direct"] == 0
+            assert np.array_equal(ps.run(torch.from_numpy(img).cuda()).cpu().numpy(), fft)
+            ps.close()
     monkeypatch.delenv("BLUR_B200_DIRECT", raising=False)
     pads = set()
     for s10 in range(4, 66):                                    # sigma 0.4 .. 6.5: every pad 1 .. 20
@@ -792,6 +807,7 @@ def test_dft_image_vs_oracle_and_golden(bb, oracle):
     # differ by 3 LSB, all on the Nyquist row with |Re F| < 1.6; everything else is within 1 LSB.
     d = np.abs(out.astype(int) - gold.astype(int))
     assert (d > 1).mean() < 1e-5 and d.max() <= 4 and d.mean() < 0.02
+    assert int((d > 1).sum()) <= 8, int((d > 1).sum())     # the contract is +-1 LSB: the exceptions are counted (4 measured), not only bounded
     ill = 10.0 ** (oracle.dft_image(im, 0.1, want_f32=True)[1] / 20.0) < 4.0      # |Re F| < 4
     assert not (d > 1)[~np.moveaxis(ill, 0, -1)].any()
     im = cv2.imread(os.path.join(GOLDEN, "spectrum_in_noise200.png"), cv2.IMREAD_COLOR)

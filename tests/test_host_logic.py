@@ -201,6 +201,15 @@ for rows, cols, sigma, mode in [(64, 96, 2.0, 0), (135, 241, 6.0, 1), (101, 75, 
     # return exchange: column stripes -> the row stripes the input came in
     back = sb.to_row_stripe()
     assert back.shape == (g.valid_rows, cols, 3) and np.array_equal(back.numpy(), single[g.row0:g.row0 + g.valid_rows]), (rows, cols)
+# ranks whose BLUR_B200_* environment differs would lay the intermediate out differently: refused loudly on every rank
+os.environ.pop("BLUR_B200_QUIRK_SHARDED", None)
+if rank == 1: os.environ["BLUR_B200_ALGO"] = "full"
+try:
+    ShardedGaussBlur(64, 96, 2.0, 0, device=torch.device("cpu"), row_pass=lambda *a: None, col_pass=lambda *a: None)
+    raise SystemExit("layout disagreement between the ranks was not detected")
+except RuntimeError as e:
+    assert "disagree" in str(e), e
+os.environ.pop("BLUR_B200_ALGO", None)
 dist.barrier()
 print("rank", rank, "ok")
 '''

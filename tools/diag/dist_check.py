@@ -1,6 +1,5 @@
 """torchrun check: sharded blur over WORLD_SIZE GPUs is bit-identical to the single-GPU blur."""
 import os, sys
-os.environ.setdefault("BLUR_B200_DIRECT", "0")   # narrow kernels: single-GPU plans would take the direct kernel, sharded ones the FFTs
 import numpy as np
 import torch
 import torch.distributed as dist
@@ -25,7 +24,7 @@ for rows, cols, sigma in cases:
     stripe = torch.from_numpy(img[g.row0:g.row0 + g.valid_rows].copy()).to(dev)
     out_cols = sb.run(stripe).clone()
     full = torch.from_numpy(img).to(dev)
-    plan = bb.GaussPlan(rows, cols, sigma, bb.NYQUIST_EXACT, device=local)
+    plan = bb.GaussPlan(rows, cols, sigma, bb.NYQUIST_EXACT, device=local, direct=False)   # narrow kernels: FFT kernels like the sharded plans
     ref = plan.run(full, torch.empty_like(full))
     mine = ref[:, g.col0:g.col0 + g.valid_cols]
     same = bool(torch.equal(mine, out_cols)) if g.valid_cols > 0 else True
@@ -35,7 +34,7 @@ for rows, cols, sigma in cases:
     # pffft mode (Nyquist corrections summed over the ranks) against the single-GPU pffft-mode plan
     if (rows, cols) != (16384, 16384) or "--headline" in sys.argv:
         sbq = ShardedGaussBlur(rows, cols, sigma, bb.NYQUIST_PFFFT, device=dev)
-        planq = bb.GaussPlan(rows, cols, sigma, bb.NYQUIST_PFFFT, device=local)
+        planq = bb.GaussPlan(rows, cols, sigma, bb.NYQUIST_PFFFT, device=local, direct=False)
         refq = planq.run(full, torch.empty_like(full))
         gotq = sbq.run(stripe)
         same = same and (bool(torch.equal(refq[:, g.col0:g.col0 + g.valid_cols], gotq)) if g.valid_cols > 0 else True)
@@ -51,7 +50,8 @@ for rows, cols, sigma in cases:
     t = torch.tensor([int(same)], device=dev)
     dist.all_reduce(t, op=dist.ReduceOp.MIN)
     if rank == 0:
-        print(f"{rows}x{cols} sigma={sigma}: algo={g.algo} stripes={g.stripe_rows} cpp={g.cpp} identical={bool(t.item())}", flush=True)
+        print(f"{rows}x{cols} sigma={sigma}: algo={g.algo} stripes={g.stripe_rows} cpp={g.cpp} identical={bool(t.item())} "
+              f"exchange={sb.exchange_mode} trial_ms={sb.exchange_trial}", flush=True)
     ok = ok and bool(t.item())
 dist.barrier()
 dist.destroy_process_group()
