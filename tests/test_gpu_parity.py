@@ -55,6 +55,24 @@ def test_gauss_vs_oracle(bb, oracle, rows, cols, sigma):
     assert lsb(out, oracle.gauss_blur_2d(img, sigma)) <= 1
 
 
+def test_pocketfft_2d_at_config4_size(bb, oracle):
+    """pocketfft_2D (Source.cpp:143-277, blur branch) at BASELINE config 4's size: 4096 x 4096, sigma 5 -> kSize 31,
+    pad 15, padded tile 4320 x 4320.  The GPU serves pocketfft_2D with the separable 1-D kernels (here the fused direct
+    kernel, and the FFT kernels with direct=False); both must stay within +-1 LSB of the oracle's true 2-D FFT path,
+    and differ from it at only a small fraction of the bytes."""
+    import torch
+    img = synth("noise", 4096, 4096, 3)
+    assert oracle.gauss_sizes(4096, 4096, 5.0)["n_row"] == 4320
+    ref = oracle.gauss_blur_2d(img, 5.0)
+    out = img.copy()
+    bb.pocketfft_2D(out, 5.0)
+    assert lsb(out, ref) <= 1 and (out != ref).mean() < 1e-3, float((out != ref).mean())
+    plan = bb.GaussPlan(4096, 4096, 5.0, 0, direct=False)
+    fft = plan.run(torch.from_numpy(img).cuda()).cpu().numpy()
+    plan.close()
+    assert lsb(fft, ref) <= 1 and (fft != ref).mean() < 1e-3, float((fft != ref).mean())
+
+
 @pytest.mark.parametrize("kind", ["const", "impulse", "stripes", "ramp"])
 def test_gauss_edge_inputs(bb, oracle, kind):
     img = synth(kind, 96, 128)
@@ -821,6 +839,19 @@ def test_dft_image_vs_oracle_and_golden(bb, oracle):
     assert lsb(out, ref_u8) <= 1
     big = ref_spec > 20.0            # |Re F| > 10: log is well conditioned there
     assert np.abs(spec - ref_spec)[big].max() < 0.05
+
+
+@pytest.mark.parametrize("radius", [10, 30, 50, 70, 90, 100])
+def test_dft_image_vs_more_reference_pairs(bb, radius):
+    """Six more of the reference's own DFT_image pairs (test_images/spectrum_analysis/blur): the full
+    1024 x 1024 input, rows [480, 544) of the reference's spectrum image (tests/golden/make_spectrum_crops.py).
+    +-1 LSB; the ill-conditioned exceptions (|Re F| ~ 1 under a DC term of 1e8, see above) are counted."""
+    cv2 = pytest.importorskip("cv2")
+    im = cv2.imread(os.path.join(GOLDEN, f"spectrum_in_blur{radius}.png"), cv2.IMREAD_COLOR)
+    gold = cv2.imread(os.path.join(GOLDEN, f"spectrum_out_blur{radius}_rows480_544.png"), cv2.IMREAD_COLOR)
+    assert im is not None and gold is not None and gold.shape == (64, im.shape[1], 3)
+    d = np.abs(bb.dft_image(im, 0.1)[480:544].astype(int) - gold.astype(int))
+    assert d.max() <= 4 and int((d > 1).sum()) <= 4 and d.mean() < 0.02, (int(d.max()), int((d > 1).sum()), float(d.mean()))
 
 
 def test_dft_image_4096_single_plane_shape(bb, oracle):
