@@ -283,7 +283,10 @@ def test_bench_reference_arm_full_size_and_threads():
     assert r.returncode == 0, r.stderr[-2000:]
     line = json.loads(r.stdout.strip().splitlines()[-1])
     cores = len(os.sched_getaffinity(0))
-    assert line["impl"] == "reference" and line["cpu_baseline"]["cores"] == cores and line["config"]["threads"] == cores
+    assert line["impl"] == "reference" and line["cpu_baseline"]["cores"] == cores and line["run"]["threads"] == cores
+    # `config` holds only what names the workload (the b200 arm prints the same dict); exact mode = Test(flag=5) -> pocketfft_1D
+    assert sorted(line["config"]) == ["cols", "l2_policy", "nyquist_mode", "rows", "sharding", "sigma", "workload"]
+    assert line["config"]["nyquist_mode"] == "exact" and "pocketfft_1D" in line["cpu_baseline"]["sample"]
     assert line["config"]["rows"] == 1080 and "1080x1920" in line["cpu_baseline"]["sample"] and "whole workload image" in line["cpu_baseline"]["sample"]
     assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["steps"] == 1 and line["warmup"] == 0
     # rank != 0 exits 0 without work
